@@ -1,0 +1,179 @@
+"""Shared base of Trainer and Inferencer (the reference's ``cyy_torch_toolbox``
+"executor" concept: a model bound to a dataset collection, a phase, a device, hooks and
+a performance metric; contract reconstructed from the call sites listed in SURVEY.md 2.3).
+"""
+from dataclasses import dataclass
+from typing import Any
+
+import torch
+from torch import nn
+
+from .dataloader import Batch, create_loader
+from .dataset import DatasetCollection
+from .hook import HookCollection
+from .hyper_parameter import HyperParameter
+from .log import get_logger
+from .metric import PerformanceMetric
+from .ml_type import ExecutorHookPoint, MachineLearningPhase
+from .model_util import ModelUtil
+
+
+@dataclass
+class HookConfig:
+    use_amp: bool = False
+    summarize_executor: bool = True
+    log_performance_metric: bool = True
+    debug: bool = False
+    use_cuda_graph: bool = True   # B200 path: capture the train step
+    use_fused_kernels: bool = True  # B200 path: flat-arena fused SGD & friends
+
+
+class ModelExecutor(HookCollection):
+    def __init__(self, model: nn.Module, dataset_collection: DatasetCollection, phase: MachineLearningPhase,
+                 hyper_parameter: HyperParameter, hook_config: HookConfig | None = None) -> None:
+        super().__init__()
+        self._model = model
+        self._model_util = ModelUtil(model)
+        self._dc = dataset_collection
+        self._phase = phase
+        self._hyper_parameter = hyper_parameter
+        self.hook_config = hook_config or HookConfig()
+        self._device = torch.device("cpu")
+        self._stream: torch.cuda.Stream | None = None
+        self._metric = PerformanceMetric()
+        self._visualizer_prefix = ""
+        self._dataloader_kwargs: dict = {}
+        self._generator: torch.Generator | None = None
+        self._seed = 0
+        self.loss_fun = nn.CrossEntropyLoss()
+
+    # ---- properties the reference reads ------------------------------------------
+    @property
+    def model(self) -> nn.Module:
+        return self._model
+
+    @property
+    def model_util(self) -> ModelUtil:
+        return self._model_util
+
+    @property
+    def dataset_collection(self) -> DatasetCollection:
+        return self._dc
+
+    @property
+    def phase(self) -> MachineLearningPhase:
+        return self._phase
+
+    @property
+    def hyper_parameter(self) -> HyperParameter:
+        return self._hyper_parameter
+
+    @property
+    def performance_metric(self) -> PerformanceMetric:
+        return self._metric
+
+    @property
+    def device(self) -> torch.device:
+        return self._device
+
+    @property
+    def dataset_size(self) -> int:
+        return self._dc.get_dataset_size(self._phase)
+
+    @property
+    def stream(self) -> torch.cuda.Stream | None:
+        return self._stream
+
+    def set_visualizer_prefix(self, prefix: str) -> None:
+        self._visualizer_prefix = prefix
+
+    def update_dataloader_kwargs(self, **kwargs: Any) -> None:
+        self._dataloader_kwargs.update(kwargs)
+
+    def set_seed(self, seed: int) -> None:
+        self._seed = seed
+        self._generator = None
+
+    # ---- device ------------------------------------------------------------------
+    def set_device(self, device: torch.device) -> None:
+        if device == self._device and (device.type != "cuda" or self._stream is not None):
+            self._model_util.to_device(device)
+            return
+        self._device = device
+        self._model_util.to_device(device)
+        self._generator = None
+        if device.type == "cuda":
+            # one stream per executor: co-located workers overlap on the GPU
+            self._stream = torch.cuda.Stream(device=device)
+        else:
+            self._stream = None
+        self._on_device_change()
+
+    def _on_device_change(self) -> None:
+        pass
+
+    def offload_from_device(self) -> None:
+        """The reference moves the model to the CPU between rounds to fit many workers
+        on a small GPU (worker/aggregation_worker.py:57,124-130).  With 180 GB of HBM3e
+        the model stays resident; only an explicit ``limited_resource`` run offloads."""
+        if getattr(self, "limited_resource", False) and self._device.type == "cuda":
+            self.wait_stream()
+            self._model_util.to_device(torch.device("cpu"))
+
+    def wait_stream(self) -> None:
+        if self._stream is not None:
+            self._stream.synchronize()
+
+    def _stream_context(self) -> Any:
+        if self._stream is not None:
+            return torch.cuda.stream(self._stream)
+        return _NullContext()
+
+    def _rng(self) -> torch.Generator:
+        if self._generator is None or self._generator.device != self._device:
+            self._generator = torch.Generator(device=self._device)
+            self._generator.manual_seed(self._seed)
+        return self._generator
+
+    def _autocast(self) -> Any:
+        if self.hook_config.use_amp:
+            return torch.autocast(device_type=self._device.type, dtype=torch.bfloat16)
+        return _NullContext()
+
+    # ---- forward -----------------------------------------------------------------
+    def _forward(self, batch: Batch) -> tuple[torch.Tensor, torch.Tensor]:
+        with self._autocast():
+            output = self._model(*batch.inputs, **{k: v for k, v in batch.kwargs.items() if k != "output_index"})
+            if "output_index" in batch.kwargs:
+                output = output[batch.kwargs["output_index"]]
+            elif batch.output_rows is not None:
+                output = output[: batch.output_rows]
+            loss = self.loss_fun(output.float(), batch.targets)
+        return output, loss
+
+    def _loader(self, phase: MachineLearningPhase) -> Any:
+        return create_loader(self._dc, phase, self._hyper_parameter.batch_size, self._device, model=self._model,
+                             generator=self._rng(), **self._dataloader_kwargs)
+
+    def _evaluate(self, phase: MachineLearningPhase) -> dict[str, float]:
+        """Loss/accuracy of the current model on ``phase`` (no grad, train-mode BN is
+        irrelevant because running stats are disabled: batch statistics are always used)."""
+        metric = PerformanceMetric()
+        was_training = self._model.training
+        self._model.eval()
+        with torch.no_grad(), self._stream_context():
+            metric.start_epoch(self._device)
+            for batch in self._loader(phase):
+                output, loss = self._forward(batch)
+                metric.add_batch(loss, output, batch.targets)
+            metric.end_epoch(1)
+        self._model.train(was_training)
+        return metric.get_epoch_metrics(1)
+
+
+class _NullContext:
+    def __enter__(self) -> None:
+        return None
+
+    def __exit__(self, *args: Any) -> None:
+        return None

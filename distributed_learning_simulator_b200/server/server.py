@@ -1,0 +1,140 @@
+"""Server base: event loop, evaluation, result fan-out, client sampling.
+
+Template-method parity with /root/reference/simulation_lib/server/server.py:20-134
+(``tester``, ``get_metric``, ``start``, ``_before_start``, ``_server_exit``,
+``_process_worker_data``, ``_before_send_result``, ``_after_send_result``,
+``_send_result``, ``_select_workers``, ``_stopped``).  The loop blocks on the endpoint
+until some pending worker has data instead of sweeping and sleeping one second
+(server.py:84-85; SURVEY.md defect D7), and a watchdog (``config.round_timeout``) turns a
+dead worker into an error instead of an endless wait.
+"""
+import copy
+import functools
+import os
+import pickle
+import random
+from typing import Any
+
+import torch
+
+from ..engine.inferencer import Inferencer
+from ..engine.log import get_logger
+from ..engine.ml_type import MachineLearningPhase
+from ..engine.tensor import TensorDict
+from ..executor import Executor
+from ..message import Message, ParameterMessage, as_flat
+from ..topology.endpoint import ServerEndpoint
+
+
+class Server(Executor):
+    def __init__(self, task_id: int | None, endpoint: ServerEndpoint, **kwargs: Any) -> None:
+        name: str = "server"
+        if task_id is not None:
+            name = f"server of {task_id}"
+        kwargs.setdefault("device_index", 0)
+        super().__init__(**kwargs, name=name)
+        self._endpoint: ServerEndpoint = endpoint
+        self.task_id = task_id
+        self._selection_rng = random.Random(self.config.reproducible_env_config.seed + 17)
+
+    @property
+    def worker_number(self) -> int:
+        return self.config.worker_number
+
+    @functools.cached_property
+    def tester(self) -> Inferencer:
+        tester = self.config.create_inferencer(phase=MachineLearningPhase.Test)
+        tester.dataset_collection.remove_dataset(phase=MachineLearningPhase.Training)
+        tester.dataset_collection.remove_dataset(phase=MachineLearningPhase.Validation)
+        tester.hook_config.summarize_executor = False
+        return tester
+
+    def _load_into_tester(self, parameter_dict: TensorDict) -> None:
+        tester = self.tester
+        tester.set_device(self._get_device())
+        flat = as_flat(parameter_dict)
+        if flat is not None and tester.model_util.flat_parameter is not None \
+                and flat.layout == tester.model_util.layout:
+            tester.model_util.load_parameter_list(flat.flat)
+        else:
+            tester.model_util.load_parameter_dict(parameter_dict)
+        tester.model_util.disable_running_stats()
+
+    def get_metric(self, parameter_dict: TensorDict | ParameterMessage, keep_performance_logger: bool = True) -> dict:
+        if isinstance(parameter_dict, ParameterMessage):
+            parameter_dict = parameter_dict.parameter
+        self._load_into_tester(parameter_dict)
+        self.tester.hook_config.log_performance_metric = keep_performance_logger
+        self.tester.inference()
+        metric: dict = self.tester.performance_metric.get_epoch_metrics(1)
+        self._release_device_lock()
+        self.tester.offload_from_device()
+        return metric
+
+    def start(self) -> None:
+        with self._get_execution_context():
+            with open(os.path.join(self.save_dir, "config.pkl"), "wb") as f:
+                pickle.dump(self.config, f)
+            self._before_start()
+            worker_set: set = set()
+            timeout = getattr(self.config, "round_timeout", None)
+            while not self._stopped():
+                if not worker_set:
+                    worker_set = set(range(self._endpoint.worker_num))
+                assert self._endpoint.worker_num == self.config.worker_number
+                ready = self._endpoint.wait_for_data(worker_set, timeout=timeout)
+                if not ready:
+                    raise TimeoutError(f"no data from workers {sorted(worker_set)} within {timeout}s")
+                for worker_id in sorted(ready):
+                    get_logger().debug("get result from %s worker_num %s", worker_id, self._endpoint.worker_num)
+                    self._process_worker_data(worker_id, self._endpoint.get(worker_id=worker_id))
+                    worker_set.remove(worker_id)
+                    if self._stopped():
+                        break
+            self._endpoint.close()
+            self._server_exit()
+            get_logger().debug("end server")
+
+    def _before_start(self) -> None:
+        pass
+
+    def _server_exit(self) -> None:
+        pass
+
+    def _process_worker_data(self, worker_id: int, data: Message) -> None:
+        raise NotImplementedError()
+
+    def _before_send_result(self, result: Message) -> None:
+        pass
+
+    def _after_send_result(self, result: Message) -> None:
+        pass
+
+    def _send_result(self, result: Message) -> None:
+        self._before_send_result(result=result)
+        if "worker_result" in result.other_data:
+            for worker_id, data in result.other_data["worker_result"].items():
+                self._endpoint.send(worker_id=worker_id, data=data)
+            self._after_unicast_result(result=result)
+            return
+        selected_workers = self._select_workers()
+        get_logger().debug("choose workers %s", selected_workers)
+        if selected_workers:
+            self._endpoint.broadcast(data=result, worker_ids=selected_workers)
+        unselected_workers = set(range(self.worker_number)) - selected_workers
+        if unselected_workers:
+            self._endpoint.broadcast(data=None, worker_ids=unselected_workers)
+        self._after_send_result(result=result)
+
+    def _after_unicast_result(self, result: Message) -> None:
+        pass
+
+    def _select_workers(self) -> set:
+        if "random_client_number" in self.config.algorithm_kwargs:
+            return set(self._selection_rng.sample(list(range(self.worker_number)),
+                                                  k=min(self.config.algorithm_kwargs["random_client_number"],
+                                                        self.worker_number)))
+        return set(range(self.worker_number))
+
+    def _stopped(self) -> bool:
+        raise NotImplementedError()
