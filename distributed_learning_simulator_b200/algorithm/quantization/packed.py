@@ -32,7 +32,10 @@ class QuantizedFlat:
 
     def compressed_bytes(self) -> int:
         t = len(self.layout.names)
-        return int(self.payload.numel() + self.aux.numel() + 4 * 3 * t)
+        payload_bytes = self.payload.numel()
+        if getattr(self, "lazy_payload_bytes", False):
+            payload_bytes = int(self.byte_offsets[-1].item())  # CUDA path over-allocates the buffer
+        return int(payload_bytes + self.aux.numel() + 4 * 3 * t)
 
     def original_bytes(self) -> int:
         return 4 * self.layout.total

@@ -1,0 +1,126 @@
+// sign_SGD packing / majority vote, FedDropoutAvg masking, FedOBD block scores.
+#include "common.cuh"
+#include "../../include/dls_b200.h"
+
+namespace dls {
+
+// 32 signs per word: bit e of word w is 1 when grad[32*w + e] < 0 (reference scaffold:
+// simulation_lib/worker/gradient_worker.py:47-48 `_process_gradient` override point)
+__global__ void __launch_bounds__(256)
+sign_pack_kernel(const float* __restrict__ grad, long long n, uint32_t* __restrict__ packed) {
+    const int lane = threadIdx.x & 31;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i - lane < n;
+         i += (long long)gridDim.x * blockDim.x) {
+        const bool neg = i < n && grad[i] < 0.f;
+        const uint32_t word = __ballot_sync(0xffffffffu, neg);
+        if (lane == 0) packed[i >> 5] = word;
+    }
+}
+
+// element-wise majority vote over K workers' packed signs: sign(sum_k s_k[i]), s in {-1,+1}
+__global__ void __launch_bounds__(256)
+sign_majority_kernel(const uint32_t* const* __restrict__ rows, int n_rows, long long n, float* __restrict__ vote) {
+    const int lane = threadIdx.x & 31;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i - lane < n;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long w = i >> 5;
+        int neg = 0;
+        for (int k = 0; k < n_rows; ++k) neg += (rows[k][w] >> lane) & 1u;  // one broadcast load per warp
+        const int s = n_rows - 2 * neg;
+        if (i < n) vote[i] = s > 0 ? 1.f : (s < 0 ? -1.f : 0.f);
+    }
+}
+
+// upload masking of FedDropoutAvg (reference: method/fed_dropout_avg/worker.py:23-27 draws a
+// Bernoulli tensor, multiplies, then count_nonzero().item() per tensor); one pass here
+__global__ void __launch_bounds__(256)
+dropout_mask_kernel(const float* __restrict__ in, long long n, float keep_prob, uint64_t seed, float* __restrict__ out,
+                    unsigned long long* __restrict__ nonzero_count) {
+    unsigned int local = 0;
+    const long long n_vec = (n + 3) >> 2;
+    for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < n_vec;
+         v += (long long)gridDim.x * blockDim.x) {
+        const uint4 r = philox4x32((uint32_t)v, (uint32_t)(v >> 32), 7u, 0u, (uint32_t)seed, (uint32_t)(seed >> 32));
+        const uint32_t rnd[4] = {r.x, r.y, r.z, r.w};
+        const long long i0 = v << 2;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            if (i0 + e < n) {
+                const float x = (u32_to_unit(rnd[e]) < keep_prob) ? in[i0 + e] : 0.f;
+                out[i0 + e] = x;
+                local += x != 0.f;
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+    if ((threadIdx.x & 31) == 0 && local) atomicAdd(nonzero_count, (unsigned long long)local);
+}
+
+// FedOBD block importance: sum over each block of (cur - prev)^2 in one pass over the arena
+// (reference: method/fed_obd/obd_algorithm.py:129-145 cats, copies to CPU and calls
+// torch.norm().item() once per block)
+__global__ void __launch_bounds__(256)
+block_sqdiff_kernel(const float* __restrict__ cur, const float* __restrict__ prev,
+                    const long long* __restrict__ tensor_offsets, const int32_t* __restrict__ block_of_tensor,
+                    int n_tensors, double* __restrict__ scores) {
+    extern __shared__ long long s_off[];
+    for (int i = threadIdx.x; i <= n_tensors; i += blockDim.x) s_off[i] = tensor_offsets[i];
+    __syncthreads();
+    const long long n = s_off[n_tensors];
+    const int lane = threadIdx.x & 31;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i - lane < n;
+         i += (long long)gridDim.x * blockDim.x) {
+        const bool valid = i < n;
+        const int b = valid ? block_of_tensor[find_segment(s_off, n_tensors, i)] : -1;
+        const float d = valid ? cur[i] - prev[i] : 0.f;
+        double sq = (double)d * d;
+        const int b0 = __shfl_sync(0xffffffffu, b, 0);
+        if (__all_sync(0xffffffffu, b == b0 || !valid) && b0 >= 0) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+            if (lane == 0) atomicAdd(scores + b0, sq);
+        } else if (valid && b >= 0) {
+            atomicAdd(scores + b, sq);
+        }
+    }
+}
+
+}  // namespace dls
+
+using namespace dls;
+
+extern "C" int dls_sign_pack(const float* grad, long long n, uint32_t* packed, void* stream) {
+    if (n < 1) return fail_msg("dls_sign_pack: empty input");
+    sign_pack_kernel<<<grid_for(n, 256, 8), 256, 0, (cudaStream_t)stream>>>(grad, n, packed);
+    DLS_LAUNCHED("sign_pack_kernel");
+    return 0;
+}
+
+extern "C" int dls_sign_majority(const uint32_t* const* rows, int n_rows, long long n, float* vote, void* stream) {
+    if (n < 1 || n_rows < 1) return fail_msg("dls_sign_majority: empty input");
+    sign_majority_kernel<<<grid_for(n, 256, 8), 256, 0, (cudaStream_t)stream>>>(rows, n_rows, n, vote);
+    DLS_LAUNCHED("sign_majority_kernel");
+    return 0;
+}
+
+extern "C" int dls_dropout_mask(const float* in, long long n, float keep_prob, uint64_t seed, float* out,
+                                unsigned long long* nonzero_count, void* stream) {
+    if (n < 1) return fail_msg("dls_dropout_mask: empty input");
+    dropout_mask_kernel<<<grid_for((n + 3) / 4, 256, 8), 256, 0, (cudaStream_t)stream>>>(in, n, keep_prob, seed, out,
+                                                                                        nonzero_count);
+    DLS_LAUNCHED("dropout_mask_kernel");
+    return 0;
+}
+
+extern "C" int dls_block_sqdiff(const float* cur, const float* prev, const long long* tensor_offsets,
+                                const int32_t* block_of_tensor, int n_tensors, int n_blocks, double* scores,
+                                void* stream) {
+    if (n_tensors < 1 || n_tensors > 5000 || n_blocks < 1) return fail_msg("dls_block_sqdiff: bad sizes");
+    cudaStream_t s = (cudaStream_t)stream;
+    DLS_CHECK(cudaMemsetAsync(scores, 0, sizeof(double) * n_blocks, s));
+    const size_t smem = (size_t)(n_tensors + 1) * sizeof(long long);
+    block_sqdiff_kernel<<<kNumSMs * 8, 256, smem, s>>>(cur, prev, tensor_offsets, block_of_tensor, n_tensors, scores);
+    DLS_LAUNCHED("block_sqdiff_kernel");
+    return 0;
+}

@@ -43,9 +43,12 @@ class SampleLoader:
         self.h2d_bytes = 0
         self._pinned: tuple[torch.Tensor, torch.Tensor] | None = None
         if storage == "pinned_host" and device.type == "cuda":
-            x = util.inputs[util.indices].contiguous().pin_memory()
-            y = util.targets[util.indices].contiguous().pin_memory()
-            self._pinned = (x, y)
+            cached = getattr(util, "_pinned_cache", None)
+            if cached is None:
+                cached = (util.inputs[util.indices].contiguous().pin_memory(),
+                          util.targets[util.indices].contiguous().pin_memory())
+                util._pinned_cache = cached
+            self._pinned = cached
 
     def __len__(self) -> int:
         return math.ceil(len(self.util) / self.batch_size)
@@ -57,8 +60,14 @@ class SampleLoader:
     def epoch_tensors(self) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
         """(x_all, y_all, order): batches are ``x_all[order[i*B:(i+1)*B]]``."""
         if self._pinned is not None:
-            x = self._pinned[0].to(self.device, non_blocking=True)
-            y = self._pinned[1].to(self.device, non_blocking=True)
+            stage = getattr(self.util, "_device_stage", None)
+            if stage is None or stage[0].device != self.device:
+                stage = (torch.empty_like(self._pinned[0], device=self.device),
+                         torch.empty_like(self._pinned[1], device=self.device))
+                self.util._device_stage = stage
+            x, y = stage
+            x.copy_(self._pinned[0], non_blocking=True)   # host -> device, every epoch
+            y.copy_(self._pinned[1], non_blocking=True)
             self.h2d_bytes += x.numel() * x.element_size() + y.numel() * y.element_size()
             n = y.shape[0]
             order = torch.arange(n, device=self.device)

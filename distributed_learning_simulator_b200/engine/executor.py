@@ -98,9 +98,11 @@ class ModelExecutor(HookCollection):
     def set_device(self, device: torch.device) -> None:
         if device == self._device and (device.type != "cuda" or self._stream is not None):
             self._model_util.to_device(device)
+            self._model_util.flatten_parameters(with_grad=False)
             return
         self._device = device
         self._model_util.to_device(device)
+        self._model_util.flatten_parameters(with_grad=False)
         self._generator = None
         if device.type == "cuda":
             # one stream per executor: co-located workers overlap on the GPU
@@ -152,7 +154,11 @@ class ModelExecutor(HookCollection):
         return output, loss
 
     def _loader(self, phase: MachineLearningPhase) -> Any:
-        return create_loader(self._dc, phase, self._hyper_parameter.batch_size, self._device, model=self._model,
+        batch_size = self._hyper_parameter.batch_size
+        if phase != MachineLearningPhase.Training:
+            batch_size = max(batch_size, int(self._hyper_parameter.extra_hyper_parameters.get(
+                "inference_batch_size", 1024)))
+        return create_loader(self._dc, phase, batch_size, self._device, model=self._model,
                              generator=self._rng(), **self._dataloader_kwargs)
 
     def _evaluate(self, phase: MachineLearningPhase) -> dict[str, float]:

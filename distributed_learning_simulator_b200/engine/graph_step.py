@@ -1,0 +1,195 @@
+"""CUDA-graph training step over the flat parameter arena (the B200 training path).
+
+One optimizer step = [gather batch] -> forward -> loss -> backward -> [fused SGD] ->
+[tick] -> [metric accumulate]; the bracketed stages are this framework's kernels
+(csrc/sgd.cu), the rest is PyTorch autograd under bf16 autocast when ``use_amp`` is on.
+The whole sequence is captured ONCE per batch size and replayed for every step of every
+round: the step's batch index, learning rate and momentum-initialised flag all live in
+device memory (``state``/``lr_table``), so nothing captured depends on a host value and
+the host only enqueues ``replay()`` -- no per-step Python dispatch of ~200 kernels, no
+synchronisation until the epoch's metrics are read.
+
+The reference's counterpart is the external ``Trainer.train()`` eager loop with
+``torch.optim.SGD`` (one ATen launch per tensor per step) invoked at
+/root/reference/simulation_lib/worker/worker.py:86-88.
+"""
+import time
+from typing import Any
+
+import torch
+
+from ..ops import runtime
+from ..ops import sgd as sgd_ops
+from .dataloader import SampleLoader
+from .log import get_logger
+from .ml_type import ExecutorHookPoint, MachineLearningPhase
+
+
+# process-wide counters read by bench.py
+REPLAY_COUNTER = [0]
+H2D_BYTES = [0]
+KERNELS_PER_REPLAY = 4  # gather_batch, sgd_step, sgd_tick, metric_accumulate
+
+
+class _CapturedStep:
+    def __init__(self) -> None:
+        self.graph: torch.cuda.CUDAGraph | None = None
+        self.x: torch.Tensor | None = None
+        self.y: torch.Tensor | None = None
+        self.grad_table: torch.Tensor | None = None
+        self.grads: list = []
+
+
+class GraphTrainStep:
+    def __init__(self, trainer: Any) -> None:
+        runtime.require()
+        self.trainer = trainer
+        self.device = trainer.device
+        self.util = trainer.model_util
+        self.flat = self.util.flatten_parameters(with_grad=False)
+        self.layout = self.util.layout
+        self.n_tensors = len(self.layout.names)
+        self.offsets = torch.tensor(self.layout.offsets, dtype=torch.int64, device=self.device)
+        self.momentum_buf = torch.zeros_like(self.flat)
+        # state: [0] lr/optimizer step, [1] momentum initialised, [2] batch index in epoch
+        self.state = torch.zeros(4, dtype=torch.int32, device=self.device)
+        self.acc = torch.zeros(3, dtype=torch.float64, device=self.device)
+        self.lr_table = torch.zeros(1, dtype=torch.float32, device=self.device)
+        self.order: torch.Tensor | None = None
+        self.steps: dict[int, _CapturedStep] = {}
+        self.fresh = True
+        H2D_BYTES[0] += loader.h2d_bytes
+        self.active = False
+        self._lr_host: torch.Tensor | None = None
+        self._host_step = 0
+        self.replays = 0
+
+    # ---- optimizer state -------------------------------------------------------------
+    def reset_optimizer_state(self, keep_schedule: bool = False) -> None:
+        if keep_schedule:
+            with torch.cuda.stream(self.trainer.stream):
+                self.state[1:2].zero_()
+        else:
+            self.fresh = True
+
+    def current_lr(self) -> float:
+        if self._lr_host is None:
+            return self.trainer.hyper_parameter.learning_rate
+        return float(self._lr_host[min(self._host_step, self._lr_host.numel() - 1)])
+
+    # ---- capture -----------------------------------------------------------------------
+    def _one_step(self, step: _CapturedStep, x_all: torch.Tensor, y_all: torch.Tensor, n_order: int) -> None:
+        t = self.trainer
+        hp = t.hyper_parameter
+        sgd_ops.gather_batch(x_all, y_all, self.order, n_order, self.state, 2, step.x, step.y)
+        with t._autocast():
+            output = t.model(step.x)
+            loss = t.loss_fun(output.float(), step.y)
+        loss.backward()
+        if step.grad_table is None:
+            step.grad_table = torch.zeros(self.n_tensors, dtype=torch.int64, device=self.device)
+        sgd_ops.sgd_step(self.flat, self.momentum_buf if hp.momentum else None, step.grad_table, self.offsets,
+                         self.n_tensors, self.lr_table, self.state, hp.weight_decay, hp.momentum)
+        sgd_ops.sgd_tick(self.state)
+        sgd_ops.metric_accumulate(output.float().contiguous(), step.y, loss.detach().reshape(1), self.acc)
+
+    def _fill_grad_table(self, step: _CapturedStep) -> None:
+        params = list(self.trainer.model.parameters())
+        step.grads = [p.grad for p in params]
+        ptrs = [0 if g is None else g.data_ptr() for g in step.grads]
+        for g in step.grads:
+            assert g is None or (g.dtype == torch.float32 and g.is_contiguous())
+        step.grad_table.copy_(torch.tensor(ptrs, dtype=torch.int64))
+
+    def _capture(self, batch: int, x_all: torch.Tensor, y_all: torch.Tensor, n_order: int) -> _CapturedStep:
+        t = self.trainer
+        assert self.trainer.hyper_parameter.optimizer_name.lower() == "sgd", "the fused step implements SGD"
+        step = _CapturedStep()
+        step.x = torch.empty((batch, *x_all.shape[1:]), dtype=x_all.dtype, device=self.device)
+        step.y = torch.empty(batch, dtype=torch.int64, device=self.device)
+        params = list(t.model.parameters())
+        # warm-up (lazy init, cuDNN heuristics) must not change the training state
+        saved = (self.flat.clone(), self.momentum_buf.clone(), self.state.clone(), self.acc.clone())
+        side = torch.cuda.Stream(device=self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                for p in params:
+                    p.grad = None
+                self._one_step(step, x_all, y_all, n_order)
+                self._fill_grad_table(step)
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        for p in params:
+            p.grad = None
+        torch.cuda.synchronize(self.device)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            self._one_step(step, x_all, y_all, n_order)
+        self._fill_grad_table(step)
+        self.flat.copy_(saved[0])
+        self.momentum_buf.copy_(saved[1])
+        self.state.copy_(saved[2])
+        self.acc.copy_(saved[3])
+        step.graph = graph
+        torch.cuda.synchronize(self.device)
+        return step
+
+    # ---- run one train() -------------------------------------------------------------
+    def run(self) -> None:
+        t = self.trainer
+        hp = t.hyper_parameter
+        loader = t._loader(MachineLearningPhase.Training)
+        assert isinstance(loader, SampleLoader)
+        self.active = True
+        batch = hp.batch_size
+        with torch.cuda.stream(t.stream):
+            x_all, y_all, order0 = loader.epoch_tensors()  # shuffled order for epoch 1
+            n = order0.numel()
+            full, rem = divmod(n, batch)
+            steps_per_epoch = full + (1 if rem else 0)
+            total_steps = hp.epoch * steps_per_epoch
+            if self.order is None or self.order.numel() < n:
+                self.order = torch.zeros(max(n, 1), dtype=torch.int64, device=self.device)
+                self.steps.clear()
+            key_full, key_rem = (batch, x_all.data_ptr(), n), (rem, x_all.data_ptr(), n)
+            if full and key_full not in self.steps:
+                self.steps[key_full] = self._capture(batch, x_all, y_all, n)
+            if rem and key_rem not in self.steps:
+                self.steps[key_rem] = self._capture(rem, x_all, y_all, n)
+            if self.fresh:
+                self.state.zero_()
+                self._host_step = 0
+                self._lr_host = hp.lr_table(total_steps)
+                if self.lr_table.numel() < self._lr_host.numel():
+                    # the captured kernels hold the table's address: grow by re-capturing
+                    self.lr_table = torch.zeros(self._lr_host.numel(), dtype=torch.float32, device=self.device)
+                    self.steps.clear()
+                    if full:
+                        self.steps[key_full] = self._capture(batch, x_all, y_all, n)
+                    if rem:
+                        self.steps[key_rem] = self._capture(rem, x_all, y_all, n)
+                self.lr_table[: self._lr_host.numel()].copy_(self._lr_host, non_blocking=True)
+                if self.lr_table.numel() > self._lr_host.numel():
+                    self.lr_table[self._lr_host.numel():].fill_(float(self._lr_host[-1]))
+                self.fresh = False
+            for epoch in range(1, hp.epoch + 1):
+                epoch_start = time.monotonic()
+                t.exec_hooks(ExecutorHookPoint.BEFORE_EPOCH, executor=t, epoch=epoch)
+                if epoch > 1:
+                    # pinned-host storage re-copies the shard into the same staging buffers
+                    order0 = loader.epoch_tensors()[2]
+                self.order[:n].copy_(order0)
+                self.state[2:3].zero_()
+                self.acc.zero_()
+                for _ in range(full):
+                    self.steps[key_full].graph.replay()
+                if rem:
+                    self.steps[key_rem].graph.replay()
+                self.replays += steps_per_epoch
+                REPLAY_COUNTER[0] += steps_per_epoch
+                self._host_step += steps_per_epoch
+                t.performance_metric.start_epoch(self.device)
+                t.performance_metric.accumulator.copy_(self.acc)
+                t._epoch_end(epoch, epoch_start)
+        H2D_BYTES[0] += loader.h2d_bytes
+        self.active = False

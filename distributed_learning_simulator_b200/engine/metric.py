@@ -9,6 +9,8 @@ import torch
 
 
 class PerformanceMetric:
+    d2h_bytes = 0  # process-wide count of metric bytes read back from the device
+
     def __init__(self) -> None:
         self._epoch_metrics: dict[int, dict[str, torch.Tensor]] = {}
         self._acc: torch.Tensor | None = None  # [loss_sum, correct, count]
@@ -38,6 +40,8 @@ class PerformanceMetric:
     def end_epoch(self, epoch: int) -> dict[str, torch.Tensor]:
         assert self._acc is not None
         acc = self._acc.cpu()
+        if self._acc.is_cuda:
+            PerformanceMetric.d2h_bytes += acc.numel() * acc.element_size()
         cnt = acc[2].clamp(min=1.0)
         m = {"loss": (acc[0] / cnt).float(), "accuracy": (acc[1] / cnt).float(), "sample_count": acc[2].float()}
         self._epoch_metrics[epoch] = m

@@ -1,0 +1,91 @@
+"""Front-ends of csrc/misc.cu: sign packing / majority vote (sign_SGD), Bernoulli upload
+masking (FedDropoutAvg), per-block squared parameter change (FedOBD)."""
+import torch
+
+from . import runtime
+
+_seed = [0x243F6A8885A308D3]
+
+
+def _next_seed() -> int:
+    _seed[0] = (_seed[0] * 6364136223846793005 + 1442695040888963407) & 0xFFFFFFFFFFFFFFFF
+    return _seed[0]
+
+
+def sign_pack(grad: torch.Tensor) -> torch.Tensor:
+    n = grad.numel()
+    if grad.is_cuda and runtime.available():
+        packed = torch.empty((n + 31) // 32, dtype=torch.int32, device=grad.device)
+        runtime.call("dls_sign_pack", grad.data_ptr(), n, packed.data_ptr(), runtime.stream_ptr(grad.device))
+        return packed
+    return oracle_sign_pack(grad)
+
+
+def oracle_sign_pack(grad: torch.Tensor) -> torch.Tensor:
+    n = grad.numel()
+    bits = (grad.reshape(-1) < 0).to(torch.int64)
+    pad = (-n) % 32
+    if pad:
+        bits = torch.cat([bits, bits.new_zeros(pad)])
+    weights = (1 << torch.arange(32, dtype=torch.int64, device=grad.device))
+    words = (bits.view(-1, 32) * weights).sum(dim=1)
+    words = torch.where(words >= 2 ** 31, words - 2 ** 32, words)
+    return words.to(torch.int32)
+
+
+def sign_majority(rows: list[torch.Tensor], n: int) -> torch.Tensor:
+    device = rows[0].device
+    if rows[0].is_cuda and runtime.available():
+        rows = [r.to(device, non_blocking=True) for r in rows]
+        table = runtime.pointer_table(rows, device)
+        vote = torch.empty(n, dtype=torch.float32, device=device)
+        runtime.call("dls_sign_majority", table.data_ptr(), len(rows), n, vote.data_ptr(), runtime.stream_ptr(device))
+        return vote
+    return oracle_sign_majority(rows, n)
+
+
+def oracle_sign_majority(rows: list[torch.Tensor], n: int) -> torch.Tensor:
+    total = torch.zeros(n, dtype=torch.int64, device=rows[0].device)
+    shifts = torch.arange(32, dtype=torch.int64, device=rows[0].device)
+    for r in rows:
+        w = r.to(torch.int64) & 0xFFFFFFFF
+        neg = ((w.view(-1, 1) >> shifts) & 1).view(-1)[:n]
+        total += 1 - 2 * neg
+    return torch.sign(total).float()
+
+
+def dropout_mask(flat: torch.Tensor, keep_prob: float, seed: int | None = None) -> tuple[torch.Tensor, torch.Tensor]:
+    """Returns (masked copy, device scalar with the number of non-zero elements)."""
+    if flat.is_cuda and runtime.available():
+        out = torch.empty_like(flat)
+        count = torch.zeros(1, dtype=torch.int64, device=flat.device)
+        runtime.call("dls_dropout_mask", flat.data_ptr(), flat.numel(), float(keep_prob),
+                     _next_seed() if seed is None else int(seed), out.data_ptr(), count.data_ptr(),
+                     runtime.stream_ptr(flat.device))
+        return out, count
+    mask = torch.bernoulli(torch.full_like(flat, keep_prob))
+    out = flat * mask
+    return out, torch.count_nonzero(out).reshape(1)
+
+
+def block_sqdiff(cur: torch.Tensor, prev: torch.Tensor, tensor_offsets: torch.Tensor, block_of_tensor: torch.Tensor,
+                 n_blocks: int) -> torch.Tensor:
+    """scores[b] = sum over the tensors of block b of (cur - prev)^2 (fp64)."""
+    if cur.is_cuda and runtime.available():
+        scores = torch.empty(n_blocks, dtype=torch.float64, device=cur.device)
+        runtime.call("dls_block_sqdiff", cur.data_ptr(), prev.data_ptr(), tensor_offsets.data_ptr(),
+                     block_of_tensor.data_ptr(), block_of_tensor.numel(), n_blocks, scores.data_ptr(),
+                     runtime.stream_ptr(cur.device))
+        return scores
+    return oracle_block_sqdiff(cur, prev, tensor_offsets, block_of_tensor, n_blocks)
+
+
+def oracle_block_sqdiff(cur, prev, tensor_offsets, block_of_tensor, n_blocks) -> torch.Tensor:
+    scores = torch.zeros(n_blocks, dtype=torch.float64, device=cur.device)
+    offs = tensor_offsets.tolist()
+    blocks = block_of_tensor.tolist()
+    d = (cur.double() - prev.double()) ** 2
+    for t, b in enumerate(blocks):
+        if b >= 0:
+            scores[b] += d[offs[t]: offs[t + 1]].sum()
+    return scores

@@ -114,6 +114,9 @@ class AggregationServer(Server):
 
     def _after_send_result(self, result: Any) -> None:
         if isinstance(result, ParameterMessageBase) and not result.in_round:
+            from ..utils.observer import notify_round_end
+
+            notify_round_end(self, self._round_number)
             self._round_number += 1
         self.__algorithm.clear_worker_data()
 

@@ -1,0 +1,104 @@
+/* C ABI of libdls_b200.so -- the hand-written sm_100a kernels of the B200-native
+ * federated-learning simulator.  Every entry point returns 0 on success or a non-zero
+ * code (see dls_last_error()).  Pointers are device pointers unless named h_*; `stream`
+ * is a cudaStream_t passed as void*.  Python binds these through ctypes
+ * (distributed_learning_simulator_b200/ops/runtime.py). */
+#ifndef DLS_B200_H
+#define DLS_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* dls_last_error(void);
+long long dls_launch_count(void);
+void dls_reset_launch_count(void);
+
+/* ---- aggregation (reference: simulation_lib/algorithm/fed_avg_algorithm.py:39-81,
+ *      message.py:41-49 restore, server/server.py:114-120 broadcast) -------------------
+ * out[i] = old_scale*old[i] + (sum_k w[k]*rows[k][i]) * inv_total  for i in [lo, hi),
+ * fp64 accumulation, written to every dsts[d] (local or peer-mapped buffers: the
+ * broadcast is fused into the reduction epilogue).  rows/dsts/weights are device arrays.
+ * If flags != NULL the kernel runs a device-side barrier over n_ranks before reading
+ * (peers' uploads are complete) and after writing (everyone's slice has landed):
+ * peer_flags[r] points at rank r's flag block (mapped locally), epoch grows by one per
+ * call.  nan_flag (uint32, device) is set to 1 if any output is NaN. */
+int dls_fedavg_reduce_f32(const float* const* rows, const float* weights, int n_rows, const float* old,
+                          float old_scale, double inv_total, float* const* dsts, int n_dsts, long long lo,
+                          long long hi, uint32_t* const* peer_flags, int n_ranks, int rank, uint32_t epoch,
+                          uint32_t* nan_flag, void* stream);
+
+/* Same reduction with per-row decode at load time: kind 0 fp32, 1 stochastic-255 packed
+ * (u8 magnitudes + sign plane + per-tensor scale), 2 NNADQ packed (per-tensor bit width);
+ * optional per-element denominators (FedDropoutAvg: weights count only non-zero
+ * uploads) and per-(row,tensor) participation bitmap (FedOBD block dropout: absent
+ * blocks contribute the old value).  Work is decomposed into (tensor, 8-element group)
+ * items so packed groups are byte aligned.  See csrc/reduce.cu for the descriptor. */
+struct DlsPackedRow {
+    const void* payload;          /* fp32 row | u8 magnitudes | packed codes           */
+    const uint8_t* aux;           /* sq: sign plane over the flat vector               */
+    const float* scale;           /* [T]                                               */
+    const float* offset;          /* [T] (nnadq)                                       */
+    const int32_t* bits;          /* [T] (nnadq)                                       */
+    const long long* byte_offsets;/* [T+1] (nnadq)                                     */
+    const uint8_t* present;       /* [T] 1 = this row carries tensor t (NULL = all)    */
+    float weight;
+    int32_t kind;
+    int32_t is_delta;             /* 1: row holds deltas (added to old), 0: absolute   */
+    int32_t pad;
+};
+int dls_fedavg_reduce_packed(const struct DlsPackedRow* rows, int n_rows, const float* old,
+                             const long long* tensor_offsets, const long long* group_offsets, int n_tensors,
+                             int nonzero_denominator, float* out, uint32_t* nan_flag, void* stream);
+
+/* ---- local SGD (reference: external torch.optim.SGD inside Trainer.train(), and
+ *      simulation_lib/worker/gradient_worker.py:13-26,96-116) --------------------------
+ * Multi-tensor fused SGD over the flat parameter arena: gradients are read through a
+ * device pointer table (one entry per tensor), weight decay, momentum/dampening/
+ * nesterov, lr = lr_table[min(state[0], lr_len-1)].  state[1] == 0 means "momentum
+ * buffer not initialised" (first step copies the gradient like torch.optim.SGD). */
+int dls_sgd_step(float* params, float* momentum_buf, const float* const* grads, const long long* tensor_offsets,
+                 int n_tensors, const float* lr_table, int lr_len, const int32_t* state, float weight_decay,
+                 float momentum, float dampening, int nesterov, void* stream);
+/* state[0] += 1 (schedule step); state[1] = 1 (momentum ready); state[2] += 1 (batch index in epoch) */
+int dls_sgd_tick(int32_t* state, void* stream);
+/* x_out[b,:] = x_all[order[state[0]*batch + b], :], y_out[b] = y_all[...]; rows past n_order repeat the last */
+int dls_gather_batch(const float* x_all, const long long* y_all, const long long* order, long long n_order,
+                     const int32_t* state, int state_index, int batch, long long row_elems, float* x_out,
+                     long long* y_out, void* stream);
+/* acc[0] += loss*batch ; acc[1] += #(argmax(logits)==y) ; acc[2] += batch   (fp64 acc) */
+int dls_metric_accumulate(const float* logits, const long long* targets, const float* loss, int batch, int classes,
+                          double* acc, void* stream);
+
+/* ---- quantizers (reference: topology/quantized_endpoint.py:76,82,89,102-104 and the
+ *      external cyy_torch_algorithm.quantization; oracle in algorithm/quantization) ---- */
+int dls_sq_quant(const float* flat, long long n, const long long* tensor_offsets, int n_tensors, int level,
+                 uint64_t seed, uint8_t* payload, uint8_t* sign_plane, float* scale, uint32_t* scratch_absmax,
+                 void* stream);
+int dls_sq_dequant(const uint8_t* payload, const uint8_t* sign_plane, const float* scale,
+                   const long long* tensor_offsets, int n_tensors, long long n, float* out, void* stream);
+/* stats scratch: [T][4] doubles (min, max, sum, sumsq) -- zeroed/initialised by the call */
+int dls_nnadq_quant(const float* flat, const long long* tensor_offsets, const long long* group_offsets, int n_tensors,
+                    float weight, double* scratch_stats, float* scale, float* offset, int32_t* bits,
+                    long long* byte_offsets, uint8_t* payload, long long payload_capacity, void* stream);
+int dls_nnadq_dequant(const uint8_t* payload, const float* scale, const float* offset, const int32_t* bits,
+                      const long long* byte_offsets, const long long* tensor_offsets, const long long* group_offsets,
+                      int n_tensors, float* out, void* stream);
+
+/* ---- sign_SGD (reference scaffold: worker/gradient_worker.py:47-48,85-94) ----------- */
+int dls_sign_pack(const float* grad, long long n, uint32_t* packed, void* stream);
+/* vote[i] = sign(sum_k sign_k[i]) in {-1,0,+1}; rows are packed sign words (1 = negative) */
+int dls_sign_majority(const uint32_t* const* rows, int n_rows, long long n, float* vote, void* stream);
+
+/* ---- FedDropoutAvg / FedOBD helpers (reference: method/fed_dropout_avg/worker.py:23-27,
+ *      method/fed_obd/obd_algorithm.py:129-145) ---------------------------------------- */
+int dls_dropout_mask(const float* in, long long n, float keep_prob, uint64_t seed, float* out,
+                     unsigned long long* nonzero_count, void* stream);
+/* scores[b] = sum over block b of (cur-prev)^2 ; block_of_tensor maps tensor -> block */
+int dls_block_sqdiff(const float* cur, const float* prev, const long long* tensor_offsets,
+                     const int32_t* block_of_tensor, int n_tensors, int n_blocks, double* scores, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,259 @@
+"""Every hand-written kernel against a plain PyTorch fp32/fp64 statement of the same op."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dev():
+    from distributed_learning_simulator_b200.ops import runtime
+
+    runtime.require()
+    return torch.device("cuda", 0)
+
+
+def _layout(numels):
+    from distributed_learning_simulator_b200.engine.model_util import ParameterLayout
+
+    return ParameterLayout([f"t{i}" for i in range(len(numels))], [torch.Size([n]) for n in numels])
+
+
+NUMELS = [1728, 64, 64, 36864, 10, 7, 1, 5120, 33, 4099]
+
+
+@pytest.mark.parametrize("k", [1, 3, 8, 17])
+@pytest.mark.parametrize("delta", [True, False])
+def test_fedavg_reduce_f32(dev, k, delta):
+    from distributed_learning_simulator_b200.ops import reduce as R
+
+    n = sum(NUMELS) + 3
+    g = torch.Generator(device="cuda").manual_seed(k)
+    rows = [torch.randn(n, device=dev, generator=g) for _ in range(k)]
+    weights = [float(100 + 7 * i) for i in range(k)]
+    old = torch.randn(n, device=dev, generator=g)
+    out = R.reduce_rows_f32(rows, weights, old if delta else None, 1.0 if delta else 0.0, 1.0 / sum(weights))
+    ref = R.oracle_reduce(rows, weights, old if delta else None, 1.0 if delta else 0.0, 1.0 / sum(weights))
+    torch.testing.assert_close(out, ref, rtol=1e-6, atol=1e-6)
+
+
+def test_fedavg_reduce_nan_flag(dev):
+    from distributed_learning_simulator_b200.ops import reduce as R
+
+    rows = [torch.randn(1000, device=dev) for _ in range(2)]
+    rows[1][17] = float("nan")
+    with pytest.raises(AssertionError):
+        R.reduce_rows_f32(rows, [1.0, 1.0], None, 0.0, 0.5)
+
+
+def test_sq_quant_roundtrip_and_unbiased(dev):
+    from distributed_learning_simulator_b200.ops import quant as Q
+
+    layout = _layout(NUMELS)
+    flat = torch.randn(layout.total, device=dev)
+    flat[layout.offsets[2]:layout.offsets[3]] *= 1e-3
+    flat[5] = 0.0
+    q = Q.sq_quant(flat, layout, 255, seed=1)
+    deq = Q.sq_dequant(q)
+    offs = layout.offsets
+    for t in range(len(NUMELS)):
+        x = flat[offs[t]:offs[t + 1]]
+        s = x.abs().max()
+        torch.testing.assert_close(q.scale[t] * 255, s, rtol=1e-6, atol=0)
+        assert (deq[offs[t]:offs[t + 1]] - x).abs().max() <= s / 255 * 1.0001 + 1e-12
+    assert deq[5] == 0
+    assert torch.equal(torch.sign(deq)[deq != 0], torch.sign(flat)[deq != 0])
+    # unbiased: average of many independent quantizations converges to x
+    acc = torch.zeros_like(flat)
+    reps = 64
+    for r in range(reps):
+        acc += Q.sq_dequant(Q.sq_quant(flat, layout, 255, seed=100 + r))
+    err = (acc / reps - flat).abs()
+    step = torch.cat([q.scale[t].expand(NUMELS[t]) for t in range(len(NUMELS))])
+    assert (err <= step * 0.5).float().mean() > 0.99
+    # torch oracle dequant understands the kernel's packing
+    from distributed_learning_simulator_b200.algorithm.quantization.packed import unpack_bits
+
+    neg = unpack_bits(q.aux.cpu(), 1, layout.total).bool()
+    assert torch.equal(neg.to(dev)[flat != 0], (flat < 0)[flat != 0])
+
+
+@pytest.mark.parametrize("weight", [0.01, 0.001, 0.0001])
+def test_nnadq_matches_oracle(dev, weight, monkeypatch):
+    from distributed_learning_simulator_b200.algorithm.quantization import deterministic as D
+    from distributed_learning_simulator_b200.ops import quant as Q
+
+    layout = _layout(NUMELS)
+    flat = torch.randn(layout.total, device=dev) * 0.05
+    flat[layout.offsets[5]:layout.offsets[6]] = 0.25  # constant tensor: zero range
+    q = Q.nnadq_quant(flat, layout, weight)
+    deq = Q.nnadq_dequant(q)
+    monkeypatch.setattr(Q, "available", lambda: False)
+    ref_q = D.nnadq_quantize_flat(flat.cpu(), layout, weight)
+    ref = D.nnadq_dequantize_flat(ref_q)
+    assert torch.equal(q.bits.cpu(), ref_q.bits)
+    assert torch.equal(q.byte_offsets.cpu(), ref_q.byte_offsets)
+    torch.testing.assert_close(q.scale.cpu(), ref_q.scale, rtol=1e-6, atol=0)
+    nbytes = int(ref_q.byte_offsets[-1])
+    same = (q.payload[:nbytes].cpu() == ref_q.payload).float().mean()
+    assert same > 0.999  # rounding ties may differ in the last ulp of the statistics
+    step = torch.cat([ref_q.scale[t].expand(NUMELS[t]) for t in range(len(NUMELS))])
+    assert ((deq.cpu() - ref).abs() <= step * 1.001 + 1e-7).all()
+    assert ((deq.cpu() - flat.cpu()).abs() <= step * 0.5001 + 1e-7).all()
+    assert q.compression_ratio() == pytest.approx(ref_q.compression_ratio(), rel=1e-6)
+
+
+@pytest.mark.parametrize("variant", ["fedavg", "dropout"])
+def test_fedavg_reduce_packed_mixed(dev, variant):
+    from distributed_learning_simulator_b200.message import DeltaParameterMessage, FlatParameter, ParameterMessage
+    from distributed_learning_simulator_b200.ops import quant as Q
+    from distributed_learning_simulator_b200.ops import reduce as R
+
+    layout = _layout(NUMELS)
+    old = FlatParameter(torch.randn(layout.total, device=dev), layout)
+    rows, msgs = [], {}
+    for k in range(5):
+        x = torch.randn(layout.total, device=dev) * 0.1
+        if variant == "dropout":
+            x = x * (torch.rand_like(x) < 0.7)
+            msgs[k] = ParameterMessage(dataset_size=10 + k, parameter=FlatParameter(x, layout))
+            rows.append((x, False))
+        elif k % 3 == 0:
+            msgs[k] = DeltaParameterMessage(dataset_size=10 + k, delta_parameter=FlatParameter(x, layout))
+            rows.append((x, True))
+        elif k % 3 == 1:
+            q = Q.sq_quant(x, layout, 255, seed=k)
+            msgs[k] = DeltaParameterMessage(dataset_size=10 + k, delta_parameter={"__quantized__": q})
+            rows.append((Q.sq_dequant(q), True))
+        else:
+            q = Q.nnadq_quant(x, layout, 0.001)
+            msgs[k] = ParameterMessage(dataset_size=10 + k, parameter={"__quantized__": q})
+            rows.append((Q.nnadq_dequant(q), False))
+    for m in msgs.values():
+        assert R.can_fuse(m, old)
+    out = R.fused_aggregate(msgs, old, variant=variant).flat
+    acc = torch.zeros(layout.total, dtype=torch.float64, device=dev)
+    den = torch.zeros(layout.total, dtype=torch.float64, device=dev)
+    for k, (x, is_delta) in enumerate(rows):
+        v = (old.flat + x if is_delta else x).double()
+        w = torch.full_like(den, float(10 + k))
+        if variant == "dropout":
+            w = w * (v != 0)
+        acc += w * v
+        den += w
+    den[den == 0] = 1
+    torch.testing.assert_close(out, (acc / den).float(), rtol=1e-5, atol=1e-6)
+
+
+def test_fedavg_reduce_packed_partial_blocks(dev):
+    """FedOBD stage 1: dropped blocks contribute the old value (ParameterMessage.complete)."""
+    from distributed_learning_simulator_b200.message import FlatParameter, ParameterMessage
+    from distributed_learning_simulator_b200.ops import reduce as R
+
+    layout = _layout(NUMELS)
+    old = FlatParameter(torch.randn(layout.total, device=dev), layout)
+    msgs, dense = {}, []
+    for k in range(3):
+        x = torch.randn(layout.total, device=dev)
+        names = [n for i, n in enumerate(layout.names) if (i + k) % 2 == 0]
+        msgs[k] = ParameterMessage(dataset_size=5 + k, parameter=R.PartialFlat(x, layout, names))
+        full = old.flat.clone()
+        for n in names:
+            full[layout.slice_of(n)] = x[layout.slice_of(n)]
+        dense.append(full)
+        assert R.can_fuse(msgs[k], old)
+    out = R.fused_aggregate(msgs, old, variant="fedavg").flat
+    ref = R.oracle_reduce(dense, [5.0, 6.0, 7.0], None, 0.0, 1.0 / 18.0)
+    torch.testing.assert_close(out, ref, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("momentum,nesterov,wd", [(0.9, False, 0.0), (0.9, True, 1e-4), (0.0, False, 5e-4)])
+def test_sgd_step_matches_torch(dev, momentum, nesterov, wd):
+    from distributed_learning_simulator_b200.ops import sgd as S
+
+    layout = _layout(NUMELS)
+    params = [torch.nn.Parameter(torch.randn(n, device=dev)) for n in NUMELS]
+    ref_opt = torch.optim.SGD(params, lr=0.1, momentum=momentum, nesterov=nesterov, weight_decay=wd)
+    flat = torch.cat([p.detach() for p in params]).clone()
+    mom = torch.zeros_like(flat)
+    offsets = torch.tensor(layout.offsets, dtype=torch.int64, device=dev)
+    lr_table = torch.tensor([0.1, 0.05, 0.025], device=dev)
+    state = torch.zeros(4, dtype=torch.int32, device=dev)
+    for step in range(3):
+        grads = [torch.randn(n, device=dev) for n in NUMELS]
+        if step == 1:
+            grads[3] = None  # a parameter without gradient is left untouched
+        for p, g in zip(params, grads):
+            p.grad = g
+        for group in ref_opt.param_groups:
+            group["lr"] = float(lr_table[step])
+        ref_opt.step()
+        table = torch.tensor([0 if g is None else g.data_ptr() for g in grads], dtype=torch.int64, device=dev)
+        S.sgd_step(flat, mom, table, offsets, len(NUMELS), lr_table, state, wd, momentum, 0.0, nesterov)
+        S.sgd_tick(state)
+        torch.cuda.synchronize()
+        ref = torch.cat([p.detach() for p in params])
+        torch.testing.assert_close(flat, ref, rtol=1e-6, atol=1e-6)
+    assert state.tolist()[:3] == [3, 1, 3]
+
+
+def test_gather_and_metric(dev):
+    from distributed_learning_simulator_b200.ops import sgd as S
+
+    x_all = torch.randn(200, 3, 8, 8, device=dev)
+    y_all = torch.randint(0, 10, (200,), device=dev)
+    order = torch.randperm(150, device=dev)
+    state = torch.zeros(4, dtype=torch.int32, device=dev)
+    state[2] = 2
+    x = torch.empty(32, 3, 8, 8, device=dev)
+    y = torch.empty(32, dtype=torch.int64, device=dev)
+    S.gather_batch(x_all, y_all, order, 150, state, 2, x, y)
+    idx = order[64:96]
+    assert torch.equal(x, x_all[idx]) and torch.equal(y, y_all[idx])
+    logits = torch.randn(32, 10, device=dev)
+    loss = torch.nn.functional.cross_entropy(logits, y).reshape(1)
+    acc = torch.zeros(3, dtype=torch.float64, device=dev)
+    S.metric_accumulate(logits, y, loss, acc)
+    S.metric_accumulate(logits, y, loss, acc)
+    correct = (logits.argmax(1) == y).sum().item()
+    torch.testing.assert_close(acc.cpu(), torch.tensor([2 * loss.item() * 32, 2.0 * correct, 64.0], dtype=torch.float64))
+
+
+def test_sign_pack_and_majority(dev):
+    from distributed_learning_simulator_b200.ops import misc as M
+
+    n = 100003
+    grads = [torch.randn(n, device=dev) for _ in range(7)]
+    packed = [M.sign_pack(g) for g in grads]
+    for g, p in zip(grads, packed):
+        assert torch.equal(p.cpu(), M.oracle_sign_pack(g.cpu()))
+    vote = M.sign_majority(packed, n)
+    ref = torch.sign(sum(torch.where(g < 0, -1.0, 1.0) for g in grads))
+    assert torch.equal(vote, ref)
+    assert torch.equal(M.oracle_sign_majority([p.cpu() for p in packed], n), ref.cpu())
+
+
+def test_dropout_mask(dev):
+    from distributed_learning_simulator_b200.ops import misc as M
+
+    x = torch.randn(1_000_003, device=dev)
+    out, cnt = M.dropout_mask(x, 0.7, seed=3)
+    kept = out != 0
+    assert torch.equal(out[kept], x[kept])
+    assert int(cnt.item()) == int(kept.sum().item())
+    assert abs(kept.float().mean().item() - 0.7) < 0.005
+    out2, _ = M.dropout_mask(x, 0.7, seed=3)
+    assert torch.equal(out, out2)
+
+
+def test_block_sqdiff(dev):
+    from distributed_learning_simulator_b200.ops import misc as M
+
+    layout = _layout(NUMELS)
+    cur = torch.randn(layout.total, device=dev)
+    prev = torch.randn(layout.total, device=dev)
+    offsets = torch.tensor(layout.offsets, dtype=torch.int64, device=dev)
+    block_of = torch.tensor([0, 0, 1, 1, 2, 2, 2, 3, 4, 4], dtype=torch.int32, device=dev)
+    got = M.block_sqdiff(cur, prev, offsets, block_of, 5)
+    ref = M.oracle_block_sqdiff(cur, prev, offsets, block_of, 5)
+    torch.testing.assert_close(got, ref, rtol=1e-10, atol=1e-10)
