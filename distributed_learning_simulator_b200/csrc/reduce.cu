@@ -21,8 +21,8 @@ std::atomic<long long> g_launch_count{0};
 thread_local char g_last_error[512] = "";
 
 // ---- device-side barrier over ranks ------------------------------------------------
-// flag block layout per rank: uint32 arrive[2][8]  (phase 0 = "my uploads are ready",
-// phase 1 = "my slice is written everywhere"); rank r writes word [phase][r] of EVERY
+// flag block layout per rank (32 uint32 words): arrive[2][8] (phase 0 = "my uploads are
+// ready", phase 1 = "my slice is written everywhere"), nan[8] at word 16, timeout at word 24; rank r writes word [phase][r] of EVERY
 // rank's block, and waits until its own block shows `epoch` in all n_ranks words.
 __device__ __forceinline__ void barrier_signal(uint32_t* const* peer_flags, int n_ranks, int rank, int phase,
                                                uint32_t epoch) {
@@ -32,8 +32,16 @@ __device__ __forceinline__ void barrier_signal(uint32_t* const* peer_flags, int 
 __device__ __forceinline__ void barrier_wait(uint32_t* const* peer_flags, int n_ranks, int rank, int phase,
                                              uint32_t epoch) {
     const uint32_t* mine = peer_flags[rank] + phase * 8;
+    // bounded wait (~20 s at 2 GHz): a dead peer must surface as an error, not hang the GPU
+    const long long t0 = clock64();
     for (int r = 0; r < n_ranks; ++r) {
-        while ((int32_t)(ld_acquire_sys(mine + r) - epoch) < 0) __nanosleep(64);
+        while ((int32_t)(ld_acquire_sys(mine + r) - epoch) < 0) {
+            __nanosleep(64);
+            if (clock64() - t0 > 40000000000LL) {
+                atomicOr(peer_flags[rank] + 24, 1u);  // word 24: "barrier timed out"
+                return;
+            }
+        }
     }
 }
 
@@ -118,6 +126,9 @@ fedavg_reduce_f32_kernel(const float* const* __restrict__ rows, const float* __r
         __syncthreads();
         if (is_last && threadIdx.x == 0) {
             *done_counter = 0;
+            // publish this slice's NaN verdict to every rank (words 16..23) so all replicas agree
+            const uint32_t verdict = *reinterpret_cast<volatile uint32_t*>(nan_flag);
+            for (int r = 0; r < n_ranks; ++r) peer_flags[r][16 + rank] = verdict;
             barrier_signal(peer_flags, n_ranks, rank, 1, epoch);
             barrier_wait(peer_flags, n_ranks, rank, 1, epoch);
         }

@@ -86,10 +86,12 @@ __global__ void sgd_tick_kernel(int32_t* state) {
 __global__ void __launch_bounds__(256)
 gather_batch_kernel(const float* __restrict__ x_all, const long long* __restrict__ y_all,
                     const long long* __restrict__ order, long long n_order, const int32_t* __restrict__ state,
-                    int state_index, int batch, long long row_elems, float* __restrict__ x_out,
+                    int state_index, int batch_stride, long long row_elems, float* __restrict__ x_out,
                     long long* __restrict__ y_out) {
     const int b = blockIdx.x;
-    long long pos = (long long)state[state_index] * batch + b;
+    // batch_stride is the epoch's regular batch size: the (smaller) last batch starts at
+    // index * stride too
+    long long pos = (long long)state[state_index] * batch_stride + b;
     if (pos >= n_order) pos = n_order - 1;
     const long long src = order[pos];
     const float* in = x_all + src * row_elems;
@@ -170,10 +172,11 @@ extern "C" int dls_sgd_tick(int32_t* state, void* stream) {
 
 extern "C" int dls_gather_batch(const float* x_all, const long long* y_all, const long long* order,
                                 long long n_order, const int32_t* state, int state_index, int batch,
-                                long long row_elems, float* x_out, long long* y_out, void* stream) {
-    if (batch < 1 || n_order < 1) return fail_msg("dls_gather_batch: empty batch or order");
+                                int batch_stride, long long row_elems, float* x_out, long long* y_out,
+                                void* stream) {
+    if (batch < 1 || n_order < 1 || batch_stride < batch) return fail_msg("dls_gather_batch: bad batch/order");
     gather_batch_kernel<<<batch, 256, 0, (cudaStream_t)stream>>>(x_all, y_all, order, n_order, state, state_index,
-                                                                 batch, row_elems, x_out, y_out);
+                                                                 batch_stride, row_elems, x_out, y_out);
     DLS_LAUNCHED("gather_batch_kernel");
     return 0;
 }

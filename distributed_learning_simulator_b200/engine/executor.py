@@ -95,10 +95,12 @@ class ModelExecutor(HookCollection):
         self._generator = None
 
     # ---- device ------------------------------------------------------------------
-    def set_device(self, device: torch.device) -> None:
+    def set_device(self, device: torch.device, stream: "torch.cuda.Stream | None" = None) -> None:
         if device == self._device and (device.type != "cuda" or self._stream is not None):
             self._model_util.to_device(device)
             self._model_util.flatten_parameters(with_grad=False)
+            if stream is not None:
+                self._stream = stream
             return
         self._device = device
         self._model_util.to_device(device)
@@ -106,10 +108,13 @@ class ModelExecutor(HookCollection):
         self._generator = None
         if device.type == "cuda":
             # one stream per executor: co-located workers overlap on the GPU
-            self._stream = torch.cuda.Stream(device=device)
+            self._stream = stream if stream is not None else torch.cuda.Stream(device=device)
         else:
             self._stream = None
         self._on_device_change()
+
+    def stream_context(self) -> Any:
+        return self._stream_context()
 
     def _on_device_change(self) -> None:
         pass

@@ -13,6 +13,7 @@ The reference's counterpart is the external ``Trainer.train()`` eager loop with
 ``torch.optim.SGD`` (one ATen launch per tensor per step) invoked at
 /root/reference/simulation_lib/worker/worker.py:86-88.
 """
+import threading
 import time
 from typing import Any
 
@@ -24,6 +25,9 @@ from .dataloader import SampleLoader
 from .log import get_logger
 from .ml_type import ExecutorHookPoint, MachineLearningPhase
 
+
+# captures are serialised; other threads keep running eager work (thread-local capture mode)
+_capture_lock = threading.Lock()
 
 # process-wide counters read by bench.py
 REPLAY_COUNTER = [0]
@@ -58,7 +62,6 @@ class GraphTrainStep:
         self.order: torch.Tensor | None = None
         self.steps: dict[int, _CapturedStep] = {}
         self.fresh = True
-        H2D_BYTES[0] += loader.h2d_bytes
         self.active = False
         self._lr_host: torch.Tensor | None = None
         self._host_step = 0
@@ -81,7 +84,8 @@ class GraphTrainStep:
     def _one_step(self, step: _CapturedStep, x_all: torch.Tensor, y_all: torch.Tensor, n_order: int) -> None:
         t = self.trainer
         hp = t.hyper_parameter
-        sgd_ops.gather_batch(x_all, y_all, self.order, n_order, self.state, 2, step.x, step.y)
+        sgd_ops.gather_batch(x_all, y_all, self.order, n_order, self.state, 2, step.x, step.y,
+                             batch_stride=hp.batch_size)
         with t._autocast():
             output = t.model(step.x)
             loss = t.loss_fun(output.float(), step.y)
@@ -102,6 +106,10 @@ class GraphTrainStep:
         step.grad_table.copy_(torch.tensor(ptrs, dtype=torch.int64))
 
     def _capture(self, batch: int, x_all: torch.Tensor, y_all: torch.Tensor, n_order: int) -> _CapturedStep:
+        with _capture_lock:
+            return self._capture_locked(batch, x_all, y_all, n_order)
+
+    def _capture_locked(self, batch: int, x_all: torch.Tensor, y_all: torch.Tensor, n_order: int) -> _CapturedStep:
         t = self.trainer
         assert self.trainer.hyper_parameter.optimizer_name.lower() == "sgd", "the fused step implements SGD"
         step = _CapturedStep()
@@ -123,7 +131,7 @@ class GraphTrainStep:
             p.grad = None
         torch.cuda.synchronize(self.device)
         graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(graph):
+        with torch.cuda.graph(graph, capture_error_mode="thread_local"):
             self._one_step(step, x_all, y_all, n_order)
         self._fill_grad_table(step)
         self.flat.copy_(saved[0])
@@ -152,6 +160,13 @@ class GraphTrainStep:
                 self.order = torch.zeros(max(n, 1), dtype=torch.int64, device=self.device)
                 self.steps.clear()
             key_full, key_rem = (batch, x_all.data_ptr(), n), (rem, x_all.data_ptr(), n)
+            if self.fresh:
+                self._lr_host = hp.lr_table(total_steps)
+                if self.lr_table.numel() < self._lr_host.numel():
+                    # the captured kernels hold the table's address: size it before capturing
+                    self.lr_table = torch.zeros(max(self._lr_host.numel(), 4096), dtype=torch.float32,
+                                                device=self.device)
+                    self.steps.clear()
             if full and key_full not in self.steps:
                 self.steps[key_full] = self._capture(batch, x_all, y_all, n)
             if rem and key_rem not in self.steps:
@@ -159,18 +174,9 @@ class GraphTrainStep:
             if self.fresh:
                 self.state.zero_()
                 self._host_step = 0
-                self._lr_host = hp.lr_table(total_steps)
-                if self.lr_table.numel() < self._lr_host.numel():
-                    # the captured kernels hold the table's address: grow by re-capturing
-                    self.lr_table = torch.zeros(self._lr_host.numel(), dtype=torch.float32, device=self.device)
-                    self.steps.clear()
-                    if full:
-                        self.steps[key_full] = self._capture(batch, x_all, y_all, n)
-                    if rem:
-                        self.steps[key_rem] = self._capture(rem, x_all, y_all, n)
-                self.lr_table[: self._lr_host.numel()].copy_(self._lr_host, non_blocking=True)
-                if self.lr_table.numel() > self._lr_host.numel():
-                    self.lr_table[self._lr_host.numel():].fill_(float(self._lr_host[-1]))
+                m = self._lr_host.numel()
+                self.lr_table[:m].copy_(self._lr_host.to(self.device, non_blocking=True))
+                self.lr_table[m:].fill_(float(self._lr_host[-1]))
                 self.fresh = False
             for epoch in range(1, hp.epoch + 1):
                 epoch_start = time.monotonic()

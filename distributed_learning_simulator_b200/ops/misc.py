@@ -84,7 +84,7 @@ def oracle_block_sqdiff(cur, prev, tensor_offsets, block_of_tensor, n_blocks) ->
     scores = torch.zeros(n_blocks, dtype=torch.float64, device=cur.device)
     offs = tensor_offsets.tolist()
     blocks = block_of_tensor.tolist()
-    d = (cur.double() - prev.double()) ** 2
+    d = (cur - prev).double() ** 2  # fp32 difference, fp64 accumulation (what the kernel does)
     for t, b in enumerate(blocks):
         if b >= 0:
             scores[b] += d[offs[t]: offs[t + 1]].sum()

@@ -115,11 +115,11 @@ def reduce_rows_f32(rows: list[torch.Tensor], weights: list[float], old: torch.T
     if out is None:
         out = torch.empty(n, dtype=torch.float32, device=device)
     row_table = runtime.pointer_table(rows, device)
-    dst_table = runtime.pointer_table([out], device)
+    dst_table = (ctypes.c_void_p * 1)(out.data_ptr())  # host array: copied into the launch arguments
     w = torch.tensor(weights, dtype=torch.float32).pin_memory().to(device, non_blocking=True)
     flag = torch.zeros(1, dtype=torch.int32, device=device)
     runtime.call("dls_fedavg_reduce_f32", row_table.data_ptr(), w.data_ptr(), len(rows), runtime.ptr(old),
-                 float(old_scale), float(inv_total), dst_table.data_ptr(), 1, 0, n, None, 1, 0, 0, flag.data_ptr(),
+                 float(old_scale), float(inv_total), dst_table, 1, 0, n, None, 1, 0, 0, flag.data_ptr(),
                  runtime.stream_ptr(device))
     if check_nan:
         _nan_check(flag)

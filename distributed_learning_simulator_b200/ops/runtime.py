@@ -33,8 +33,8 @@ _SIGNATURES = {
     "dls_sgd_step": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_float, c_float,
                      c_float, c_int, c_void_p],
     "dls_sgd_tick": [c_void_p, c_void_p],
-    "dls_gather_batch": [c_void_p, c_void_p, c_void_p, c_ll, c_void_p, c_int, c_int, c_ll, c_void_p, c_void_p,
-                         c_void_p],
+    "dls_gather_batch": [c_void_p, c_void_p, c_void_p, c_ll, c_void_p, c_int, c_int, c_int, c_ll, c_void_p,
+                         c_void_p, c_void_p],
     "dls_metric_accumulate": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p],
     "dls_sq_quant": [c_void_p, c_ll, c_void_p, c_int, c_int, c_u64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
     "dls_sq_dequant": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_ll, c_void_p, c_void_p],
@@ -42,6 +42,12 @@ _SIGNATURES = {
                         c_void_p, c_void_p, c_ll, c_void_p],
     "dls_nnadq_dequant": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p,
                           c_void_p],
+    "dls_ipc_alloc": [c_ll, ctypes.POINTER(c_void_p)],
+    "dls_ipc_free": [c_void_p],
+    "dls_ipc_get_handle": [c_void_p, ctypes.c_char_p],
+    "dls_ipc_open_handle": [ctypes.c_char_p, ctypes.POINTER(c_void_p)],
+    "dls_ipc_close_handle": [c_void_p],
+    "dls_enable_peer_access": [c_int, c_int],
     "dls_sign_pack": [c_void_p, c_ll, c_void_p, c_void_p],
     "dls_sign_majority": [c_void_p, c_int, c_ll, c_void_p, c_void_p],
     "dls_dropout_mask": [c_void_p, c_ll, c_float, c_u64, c_void_p, c_void_p, c_void_p],

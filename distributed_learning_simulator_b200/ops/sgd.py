@@ -20,11 +20,12 @@ def sgd_tick(state: torch.Tensor) -> None:
 
 
 def gather_batch(x_all: torch.Tensor, y_all: torch.Tensor, order: torch.Tensor, n_order: int, state: torch.Tensor,
-                 state_index: int, x_out: torch.Tensor, y_out: torch.Tensor) -> None:
+                 state_index: int, x_out: torch.Tensor, y_out: torch.Tensor, batch_stride: int | None = None) -> None:
     batch = x_out.shape[0]
     row = x_out[0].numel()
     runtime.call("dls_gather_batch", x_all.data_ptr(), y_all.data_ptr(), order.data_ptr(), int(n_order),
-                 state.data_ptr(), int(state_index), int(batch), int(row), x_out.data_ptr(), y_out.data_ptr(),
+                 state.data_ptr(), int(state_index), int(batch), int(batch_stride or batch), int(row),
+                 x_out.data_ptr(), y_out.data_ptr(),
                  runtime.stream_ptr(x_out.device))
 
 

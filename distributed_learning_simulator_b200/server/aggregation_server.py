@@ -58,7 +58,7 @@ class AggregationServer(Server):
             with open(os.path.join(init_global_model_path), "rb") as f:
                 return pickle.load(f)
         tester = self.tester
-        tester.set_device(self._get_device())
+        tester.set_device(self._get_device(), stream=self._server_stream())
         from ..message import FlatParameter
 
         flat = tester.model_util.flat_parameter

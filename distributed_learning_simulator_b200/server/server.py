@@ -51,7 +51,7 @@ class Server(Executor):
 
     def _load_into_tester(self, parameter_dict: TensorDict) -> None:
         tester = self.tester
-        tester.set_device(self._get_device())
+        tester.set_device(self._get_device(), stream=self._server_stream())
         flat = as_flat(parameter_dict)
         if flat is not None and tester.model_util.flat_parameter is not None \
                 and flat.layout == tester.model_util.layout:
@@ -59,6 +59,22 @@ class Server(Executor):
         else:
             tester.model_util.load_parameter_dict(parameter_dict)
         tester.model_util.disable_running_stats()
+
+    def _server_stream(self) -> Any:
+        device = self._get_device()
+        if device.type != "cuda":
+            return None
+        if getattr(self, "_stream", None) is None:
+            self._stream = torch.cuda.Stream(device=device)
+        return self._stream
+
+    def _stream_context(self) -> Any:
+        stream = self._server_stream()
+        if stream is None:
+            import contextlib
+
+            return contextlib.nullcontext()
+        return torch.cuda.stream(stream)
 
     def get_metric(self, parameter_dict: TensorDict | ParameterMessage, keep_performance_logger: bool = True) -> dict:
         if isinstance(parameter_dict, ParameterMessage):
@@ -72,7 +88,7 @@ class Server(Executor):
         return metric
 
     def start(self) -> None:
-        with self._get_execution_context():
+        with self._get_execution_context(), self._stream_context():
             with open(os.path.join(self.save_dir, "config.pkl"), "wb") as f:
                 pickle.dump(self.config, f)
             self._before_start()

@@ -62,21 +62,24 @@ class Worker(Executor):
         self._round_num = 1
         self._force_stop = False
         with self._get_execution_context():
-            while not self._stopped():
-                if first_training:
-                    self.trainer.set_device(self._get_device())
-                    self._before_training()
-                    first_training = False
-                    # in case worker changes round number
-                    if self._stopped():
-                        break
-                else:
-                    self.trainer.hook_config.summarize_executor = False
-                    self.trainer.set_device(self._get_device())
-                self.trainer.disable_hook("batch_loss_logger")
-                self.trainer.set_visualizer_prefix(prefix=f"round: {self._round_num},")
-                self.trainer.train(**kwargs)
-                self._round_num += 1
+            self.trainer.set_device(self._get_device())
+            # every device operation of this worker (loading the global model, training,
+            # building the upload) is ordered on the worker's own stream
+            with self.trainer.stream_context():
+                while not self._stopped():
+                    if first_training:
+                        self._before_training()
+                        first_training = False
+                        # in case worker changes round number
+                        if self._stopped():
+                            break
+                    else:
+                        self.trainer.hook_config.summarize_executor = False
+                    self.trainer.disable_hook("batch_loss_logger")
+                    self.trainer.set_visualizer_prefix(prefix=f"round: {self._round_num},")
+                    self.trainer.train(**kwargs)
+                    self._round_num += 1
+                self.trainer.wait_stream()
             get_logger().debug("finish worker")
             self._endpoint.close()
             self._after_training()

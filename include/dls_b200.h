@@ -18,7 +18,8 @@ void dls_reset_launch_count(void);
  *      message.py:41-49 restore, server/server.py:114-120 broadcast) -------------------
  * out[i] = old_scale*old[i] + (sum_k w[k]*rows[k][i]) * inv_total  for i in [lo, hi),
  * fp64 accumulation, written to every dsts[d] (local or peer-mapped buffers: the
- * broadcast is fused into the reduction epilogue).  rows/dsts/weights are device arrays.
+ * broadcast is fused into the reduction epilogue).  rows/weights are device arrays; dsts is a
+ * HOST array of n_dsts device pointers (it travels in the launch arguments).
  * If flags != NULL the kernel runs a device-side barrier over n_ranks before reading
  * (peers' uploads are complete) and after writing (everyone's slice has landed):
  * peer_flags[r] points at rank r's flag block (mapped locally), epoch grows by one per
@@ -51,6 +52,15 @@ int dls_fedavg_reduce_packed(const struct DlsPackedRow* rows, int n_rows, const 
                              const long long* tensor_offsets, const long long* group_offsets, int n_tensors,
                              int nonzero_denominator, float* out, uint32_t* nan_flag, void* stream);
 
+/* ---- peer-mapped buffers for one-process-per-GPU runs (reference transport:
+ *      simulation_lib/algorithm_factory.py:26-28, pickled CPU tensors over pipes) -------- */
+int dls_ipc_alloc(long long bytes, void** out_ptr);               /* cudaMalloc + zero        */
+int dls_ipc_free(void* ptr);
+int dls_ipc_get_handle(void* ptr, unsigned char* handle_out64);   /* cudaIpcGetMemHandle      */
+int dls_ipc_open_handle(const unsigned char* handle64, void** out_ptr);
+int dls_ipc_close_handle(void* ptr);
+int dls_enable_peer_access(int device, int peer);
+
 /* ---- local SGD (reference: external torch.optim.SGD inside Trainer.train(), and
  *      simulation_lib/worker/gradient_worker.py:13-26,96-116) --------------------------
  * Multi-tensor fused SGD over the flat parameter arena: gradients are read through a
@@ -62,10 +72,11 @@ int dls_sgd_step(float* params, float* momentum_buf, const float* const* grads, 
                  float momentum, float dampening, int nesterov, void* stream);
 /* state[0] += 1 (schedule step); state[1] = 1 (momentum ready); state[2] += 1 (batch index in epoch) */
 int dls_sgd_tick(int32_t* state, void* stream);
-/* x_out[b,:] = x_all[order[state[0]*batch + b], :], y_out[b] = y_all[...]; rows past n_order repeat the last */
+/* x_out[b,:] = x_all[order[state[state_index]*batch_stride + b], :] for b < batch, y likewise;
+ * positions past n_order repeat the last entry */
 int dls_gather_batch(const float* x_all, const long long* y_all, const long long* order, long long n_order,
-                     const int32_t* state, int state_index, int batch, long long row_elems, float* x_out,
-                     long long* y_out, void* stream);
+                     const int32_t* state, int state_index, int batch, int batch_stride, long long row_elems,
+                     float* x_out, long long* y_out, void* stream);
 /* acc[0] += loss*batch ; acc[1] += #(argmax(logits)==y) ; acc[2] += batch   (fp64 acc) */
 int dls_metric_accumulate(const float* logits, const long long* targets, const float* loss, int batch, int classes,
                           double* acc, void* stream);

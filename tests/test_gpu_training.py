@@ -20,6 +20,8 @@ def test_graph_step_matches_eager():
     from distributed_learning_simulator_b200 import load_config_from_dict
     from distributed_learning_simulator_b200.engine.ml_type import MachineLearningPhase
 
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
     finals = []
     for use_graph in (True, False):
         config = load_config_from_dict(_conf(use_cuda_graph=use_graph))
