@@ -361,3 +361,83 @@ extern "C" int dls_nnadq_dequant(const uint8_t* payload, const float* scale, con
     DLS_LAUNCHED("nnadq_dequant_kernel");
     return 0;
 }
+
+// ---------------------------------------------------------------------------------------
+// dls_sq_quant_noalloc: the stochastic quantizer for callers that cannot allocate.
+//
+// dls_sq_quant needs one uint32 of scratch per tensor (the abs-max reduction target) and
+// leaves it to the caller to provide that memory.  Some callers have no way to get it:
+//   * a host that drives this library through the C ABI alone (no torch, no pooling
+//     allocator of its own) and runs with every byte of HBM already handed out to the
+//     packed workers' arenas -- a late cudaMalloc there can simply fail;
+//   * a worker thread on a GPU it shares with many other workers' streams: cudaMalloc and
+//     cudaFree are device-wide operations that stall every one of those streams, so the
+//     per-round upload path must not contain them.
+// For them the scratch lives in the library image itself: one file-scope __device__ array
+// of DLS_SQ_NOALLOC_MAX_TENSORS words (16 KiB).  Every GPU that loads the library carries
+// its own copy of that array until the process exits.
+//
+// Rules that follow from sharing one array:
+//   * n_tensors above DLS_SQ_NOALLOC_MAX_TENSORS is refused with an error, nothing runs;
+//   * the array keeps whatever the previous call left in it, so each call first zeroes the
+//     n_tensors words it is going to use (on `stream`, ahead of its kernels);
+//   * two calls whose GPU work overlaps (different streams, or different host threads on
+//     the same device) would reduce into the same words and corrupt each other's scales:
+//     callers must order them, e.g. by issuing them on one stream;
+//   * the first call on a device looks the array's device address up with
+//     cudaGetSymbolAddress (in host code the array's name is only a host-side handle, not
+//     something a kernel may dereference) and remembers it per device.  Make that first
+//     call, on every device you use, before you begin any stream capture.
+// The entry point itself never calls cudaMalloc, cudaFree or any allocating routine.
+// It has no counterpart in the reference (which has no native code at all).
+#define DLS_SQ_NOALLOC_MAX_TENSORS 4096
+
+static __device__ __align__(256) uint32_t g_sq_noalloc_scratch[DLS_SQ_NOALLOC_MAX_TENSORS];
+
+#include <mutex>
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mutex;
+uint32_t* g_noalloc_scratch_addr[kMaxDevices] = {nullptr};  // per device: address of that device's copy
+}  // namespace
+
+extern "C" int dls_sq_quant_noalloc_max_tensors(void) { return DLS_SQ_NOALLOC_MAX_TENSORS; }
+
+extern "C" int dls_sq_quant_noalloc(const float* flat, long long n, const long long* tensor_offsets, int n_tensors,
+                                    int level, uint64_t seed, uint8_t* payload, uint8_t* sign_plane, float* scale,
+                                    void* stream) {
+    if (n < 1 || n_tensors < 1) return fail_msg("dls_sq_quant_noalloc: bad sizes");
+    if (n_tensors > DLS_SQ_NOALLOC_MAX_TENSORS) {
+        snprintf(g_last_error, sizeof(g_last_error),
+                 "dls_sq_quant_noalloc: %d tensors exceed the built-in scratch of %d tensors; "
+                 "use dls_sq_quant with caller-provided scratch",
+                 n_tensors, DLS_SQ_NOALLOC_MAX_TENSORS);
+        return -1;
+    }
+    if (level < 1 || level > 255) return fail_msg("dls_sq_quant_noalloc: level must be in [1, 255]");
+    int dev = -1;
+    DLS_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) return fail_msg("dls_sq_quant_noalloc: device index out of range");
+    uint32_t* scratch = nullptr;
+    {
+        // one-time set-up per device, with that device current (it is: we just asked for it)
+        std::lock_guard<std::mutex> guard(g_noalloc_mutex);
+        if (g_noalloc_scratch_addr[dev] == nullptr) {
+            uint32_t* addr = nullptr;
+            DLS_CHECK(cudaGetSymbolAddress((void**)&addr, g_sq_noalloc_scratch));
+            if (addr == nullptr) return fail_msg("dls_sq_quant_noalloc: cudaGetSymbolAddress returned NULL");
+            g_noalloc_scratch_addr[dev] = addr;
+        }
+        scratch = g_noalloc_scratch_addr[dev];
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t smem = (size_t)(n_tensors + 1) * sizeof(long long);
+    // the array still holds the previous call's maxima: clear the words this call reduces into
+    DLS_CHECK(cudaMemsetAsync(scratch, 0, sizeof(uint32_t) * n_tensors, s));
+    sq_absmax_kernel<<<grid_for(n, 256, 8), 256, smem, s>>>(flat, n, tensor_offsets, n_tensors, scratch);
+    DLS_LAUNCHED("sq_absmax_kernel");
+    sq_pack_kernel<<<grid_for((n + 7) / 8, 256, 8), 256, smem, s>>>(flat, n, tensor_offsets, n_tensors, level, seed,
+                                                                     scratch, payload, sign_plane, scale);
+    DLS_LAUNCHED("sq_pack_kernel");
+    return 0;
+}

@@ -86,6 +86,19 @@ int dls_metric_accumulate(const float* logits, const long long* targets, const f
 int dls_sq_quant(const float* flat, long long n, const long long* tensor_offsets, int n_tensors, int level,
                  uint64_t seed, uint8_t* payload, uint8_t* sign_plane, float* scale, uint32_t* scratch_absmax,
                  void* stream);
+/* Same quantizer, same outputs, but for callers that cannot allocate device memory: a
+ * C-ABI host whose HBM is already fully handed out (a late cudaMalloc may fail), or a
+ * worker sharing its GPU with many other streams (cudaMalloc/cudaFree stall all of them).
+ * The per-tensor scratch is a 16 KiB array built into the library (one copy per GPU, held
+ * until exit) instead of a caller buffer, so n_tensors is limited to
+ * dls_sq_quant_noalloc_max_tensors() (4096); larger models are refused with an error.
+ * All calls share that array: it is cleared at the start of each call, and calls whose GPU
+ * work overlaps race -- keep them on one stream.  The first call on each device resolves
+ * the array's address (cudaGetSymbolAddress); issue it before any stream capture begins.
+ * Nothing in this entry point allocates or frees.  No counterpart in the reference. */
+int dls_sq_quant_noalloc(const float* flat, long long n, const long long* tensor_offsets, int n_tensors, int level,
+                         uint64_t seed, uint8_t* payload, uint8_t* sign_plane, float* scale, void* stream);
+int dls_sq_quant_noalloc_max_tensors(void);
 int dls_sq_dequant(const uint8_t* payload, const uint8_t* sign_plane, const float* scale,
                    const long long* tensor_offsets, int n_tensors, long long n, float* out, void* stream);
 /* stats scratch: [T][4] doubles (min, max, sum, sumsq) -- zeroed/initialised by the call */
