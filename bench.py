@@ -139,14 +139,20 @@ def run_ours(args) -> dict:
             t = torch.tensor([ms], dtype=torch.float64, device="cuda")
             torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
             ms = float(t.item())
+        h2d = graph_step.H2D_BYTES[0]
+        d2h = PerformanceMetric.d2h_bytes
+        if world > 1:
+            t = torch.tensor([h2d, d2h], dtype=torch.float64, device="cuda")
+            torch.distributed.all_reduce(t)
+            h2d, d2h = float(t[0].item()), float(t[1].item())
         samples = TRAIN_PER_WORKER * n_workers * args.steps
         replays = graph_step.REPLAY_COUNTER[0] - replay0[0]
         results[mode] = {
             "ms": ms, "samples_per_s": samples / (ms / 1e3), "rounds_per_s": args.steps / (ms / 1e3),
             "wall_ms": (timer.wall[1] - timer.wall[0]) * 1e3, "clocks": clocks,
             "launches": (timer.launches[1] - timer.launches[0]) + replays * graph_step.KERNELS_PER_REPLAY,
-            "h2d_bytes_per_step": graph_step.H2D_BYTES[0] / max(rounds, 1) if storage == "pinned_host" else 0,
-            "d2h_bytes_per_step": PerformanceMetric.d2h_bytes / max(rounds, 1),
+            "h2d_bytes_per_step": h2d / max(rounds, 1) if storage == "pinned_host" else 0,
+            "d2h_bytes_per_step": d2h / max(rounds, 1),
         }
         graph_step.H2D_BYTES[0] = 0
     dev, e2e = results["device"], results["e2e"]

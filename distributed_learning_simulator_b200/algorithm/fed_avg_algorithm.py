@@ -54,6 +54,9 @@ class FedAVGAlgorithm(AggregationAlgorithm):
                 self._all_worker_data[worker_id] = worker_data
                 return
         self.__flush_pending()
+        from ..ops import reduce as reduce_ops
+
+        worker_data = reduce_ops.materialize(worker_data)  # arena / packed payloads -> local tensors
         worker_data = self._process_worker_data(worker_data=worker_data, old_parameter_dict=old_parameter_dict)
         self._all_worker_data[worker_id] = worker_data
         if not self.accumulate or not isinstance(worker_data, ParameterMessage):

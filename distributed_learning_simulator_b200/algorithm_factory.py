@@ -17,6 +17,12 @@ from .topology.topology import ProcessPipeCentralTopology, ThreadCentralTopology
 
 def create_topology(config: Any) -> Any:
     kind = getattr(config, "topology", "auto")
+    from .parallel import context as dist_context
+
+    if dist_context.is_distributed() and kind in ("auto", "device"):
+        from .parallel.topology import DistributedTopology
+
+        return DistributedTopology(worker_num=config.worker_number, ctx=dist_context.get_context())
     if kind in ("auto", "thread", "device"):
         return ThreadCentralTopology(worker_num=config.worker_number)
     if kind == "pipe":

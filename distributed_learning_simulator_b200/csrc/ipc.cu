@@ -65,3 +65,9 @@ int dls_enable_peer_access(int device, int peer) {
 }
 
 }  // extern "C"
+
+// plain device-to-device copy whose source may be a peer-mapped pointer
+extern "C" int dls_copy_device(void* dst, const void* src, long long bytes, void* stream) {
+    DLS_CHECK(cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return 0;
+}

@@ -6,6 +6,7 @@ server/server.py:34, executor.py:62 and the key inventory in SURVEY.md 5.6).
 """
 import os
 import random
+import threading
 from dataclasses import dataclass, field
 from typing import Any
 
@@ -44,6 +45,8 @@ class ReproducibleEnvConfig:
     make_reproducible_env: bool = True
     seed: int = 0
 
+
+_model_init_lock = threading.Lock()
 
 _HYPER_KEYS = ("epoch", "batch_size", "learning_rate", "weight_decay", "momentum", "optimizer_name",
                "learning_rate_scheduler_name", "extra_hyper_parameters")
@@ -122,13 +125,15 @@ class Config:
         return create_dataset_collection(self.dc_config.dataset_name, self.dc_config.dataset_kwargs)
 
     def _create_model(self, dc: DatasetCollection) -> torch.nn.Module:
-        # every executor of a run starts from the same initial weights
-        state = torch.random.get_rng_state()
-        torch.manual_seed(self.reproducible_env_config.seed + 1)
-        try:
-            return create_model(self.model_config.model_name, dc, **self.model_config.model_kwargs)
-        finally:
-            torch.random.set_rng_state(state)
+        # every executor of a run starts from the same initial weights; the global torch RNG is
+        # process-wide, so concurrent role threads must not interleave here
+        with _model_init_lock:
+            state = torch.random.get_rng_state()
+            torch.manual_seed(self.reproducible_env_config.seed + 1)
+            try:
+                return create_model(self.model_config.model_name, dc, **self.model_config.model_kwargs)
+            finally:
+                torch.random.set_rng_state(state)
 
     def _hook_config(self) -> HookConfig:
         import copy

@@ -166,17 +166,21 @@ class ModelExecutor(HookCollection):
         return create_loader(self._dc, phase, batch_size, self._device, model=self._model,
                              generator=self._rng(), **self._dataloader_kwargs)
 
-    def _evaluate(self, phase: MachineLearningPhase) -> dict[str, float]:
+    def _evaluate(self, phase: MachineLearningPhase, reducer: Any = None) -> dict[str, float]:
         """Loss/accuracy of the current model on ``phase`` (no grad, train-mode BN is
-        irrelevant because running stats are disabled: batch statistics are always used)."""
+        irrelevant because running stats are disabled: batch statistics are always used).
+        ``reducer`` (a distributed context) sums the counters over ranks first."""
         metric = PerformanceMetric()
         was_training = self._model.training
         self._model.eval()
         with torch.no_grad(), self._stream_context():
             metric.start_epoch(self._device)
-            for batch in self._loader(phase):
-                output, loss = self._forward(batch)
-                metric.add_batch(loss, output, batch.targets)
+            if self._dc.get_dataset_size(phase) > 0:
+                for batch in self._loader(phase):
+                    output, loss = self._forward(batch)
+                    metric.add_batch(loss, output, batch.targets)
+            if reducer is not None:
+                reducer.all_reduce_sum(metric.accumulator)
             metric.end_epoch(1)
         self._model.train(was_training)
         return metric.get_epoch_metrics(1)

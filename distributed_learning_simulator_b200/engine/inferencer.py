@@ -22,10 +22,17 @@ class Inferencer(ModelExecutor):
                  hyper_parameter: HyperParameter, hook_config: HookConfig | None = None) -> None:
         super().__init__(model, dataset_collection, phase, hyper_parameter, hook_config)
         self.evaluator: Any = None  # optional hand-written batched evaluator (ops.eval)
+        self._reducer: Any = None
+
+    def shard(self, rank: int, world: int, reducer: Any) -> None:
+        """Keep every ``world``-th sample of the phase; ``inference`` then sums over ranks."""
+        util = self._dc.get_dataset_util(self._phase)
+        self._dc.set_subset(self._phase, util.indices[rank::world])
+        self._reducer = reducer
 
     def inference(self, **kwargs: Any) -> None:
         start = time.monotonic()
-        metric = self._evaluate(self._phase)
+        metric = self._evaluate(self._phase, reducer=self._reducer)
         self._metric.set_epoch_metrics(1, metric["loss"], metric["accuracy"], float(self.dataset_size))
         if self.hook_config.log_performance_metric:
             get_logger().info("%s%s in %.3f s, %s loss: %e, accuracy: %.2f%%", self._visualizer_prefix,

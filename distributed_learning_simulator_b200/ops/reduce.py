@@ -45,12 +45,19 @@ def _is_quantized(payload: Any) -> bool:
     return isinstance(payload, dict) and "__quantized__" in payload
 
 
+def _is_arena(payload: Any) -> bool:
+    return type(payload).__name__ == "ArenaPayload"
+
+
 def can_fuse(worker_data: Any, old_parameter_dict: Any) -> bool:
     if not runtime.available():
         return False
     payload, is_delta = _payload_of(worker_data)
     if payload is None or getattr(worker_data, "dataset_size", 0) <= 0:
         return False
+    if _is_arena(payload):
+        old = as_flat(old_parameter_dict) if old_parameter_dict is not None else None
+        return not is_delta or (old is not None and old.flat.is_cuda and old.layout == payload.layout)
     old = as_flat(old_parameter_dict) if old_parameter_dict is not None else None
     if old_parameter_dict is not None and (old is None or not old.flat.is_cuda):
         return False
@@ -70,6 +77,15 @@ def can_fuse(worker_data: Any, old_parameter_dict: Any) -> bool:
 def materialize(worker_data: Any) -> Any:
     """Undo lazy packing so the generic torch path can consume the message."""
     payload, is_delta = _payload_of(worker_data)
+    if _is_arena(payload):
+        from ..parallel import context as dist_context
+
+        new = payload.to_local(dist_context.get_context())
+        if is_delta:
+            worker_data.delta_parameter = new
+        else:
+            worker_data.parameter = new
+        return worker_data
     if _is_quantized(payload):
         q = payload["__quantized__"]
         from ..algorithm.quantization.deterministic import nnadq_dequantize_flat
@@ -132,6 +148,17 @@ def fused_aggregate(pending: dict, old_parameter_dict: Any, variant: str) -> Fla
     payloads = [_payload_of(m) for m in msgs]
     weights = [float(m.dataset_size) for m in msgs]
     total = sum(weights)
+    if all(_is_arena(p) for p, _ in payloads) and variant == "fedavg" and len({d for _, d in payloads}) == 1:
+        from ..parallel import context as dist_context
+
+        is_delta = payloads[0][1]
+        return dist_context.get_context().p2p_reduce(
+            [p for p, _ in payloads], weights, old.flat if (is_delta and old is not None) else None,
+            1.0 if is_delta else 0.0, 1.0 / total)
+    if any(_is_arena(p) for p, _ in payloads):
+        for m in msgs:
+            materialize(m)
+        payloads = [_payload_of(m) for m in msgs]
     plain = all(as_flat(p) is not None for p, _ in payloads) and variant == "fedavg"
     if plain and len({d for _, d in payloads}) == 1:
         is_delta = payloads[0][1]

@@ -1,0 +1,219 @@
+"""Per-process distributed context: one rank per GPU under ``torch.distributed``.
+
+NCCL (via torch.distributed) is the plumbing: rendezvous, tiny metric all-reduces, the
+gloo side group for pickled control messages.  The parameter hot path does not use it:
+uploads live in peer-mapped arenas (``csrc/ipc.cu``) and ``p2p_reduce`` launches the
+hand-written reduce kernel, in which every rank reduces its own ``[lo, hi)`` slice by
+loading all ranks' rows over NVLink and stores the result into every rank's global-model
+buffer, with device-side flag barriers on both sides (``csrc/reduce.cu``).
+"""
+import ctypes
+import os
+import threading
+from typing import Any
+
+import torch
+import torch.distributed as dist
+
+from ..engine.log import get_logger
+from ..engine.model_util import FlatParameter, ParameterLayout
+from ..ops import runtime
+
+_lock = threading.Lock()
+_current: "DistributedContext | None" = None
+
+
+def is_distributed() -> bool:
+    return int(os.environ.get("WORLD_SIZE", "1")) > 1 and os.environ.get("DLS_DISABLE_DISTRIBUTED", "0") != "1"
+
+
+def current() -> "DistributedContext | None":
+    return _current
+
+
+def get_context() -> "DistributedContext":
+    global _current
+    with _lock:
+        if _current is None:
+            _current = DistributedContext()
+    return _current
+
+
+class SymmetricBuffer:
+    """``nbytes`` of zeroed device memory on every rank, each mapped into every process."""
+
+    def __init__(self, ctx: "DistributedContext", nbytes: int) -> None:
+        self.nbytes = int(nbytes)
+        self.ctx = ctx
+        lib = runtime.require()
+        local = ctypes.c_void_p()
+        rc = lib.dls_ipc_alloc(self.nbytes, ctypes.byref(local))
+        if rc != 0:
+            raise RuntimeError(lib.dls_last_error().decode())
+        self.local_ptr = int(local.value)
+        handle = ctypes.create_string_buffer(64)
+        rc = lib.dls_ipc_get_handle(self.local_ptr, handle)
+        if rc != 0:
+            raise RuntimeError(lib.dls_last_error().decode())
+        handles: list[Any] = [None] * ctx.world
+        dist.all_gather_object(handles, bytes(handle.raw), group=ctx.control)
+        self.ptrs: list[int] = []
+        for r, h in enumerate(handles):
+            if r == ctx.rank:
+                self.ptrs.append(self.local_ptr)
+                continue
+            peer = ctypes.c_void_p()
+            rc = lib.dls_ipc_open_handle(h, ctypes.byref(peer))
+            if rc != 0:
+                raise RuntimeError(f"cannot map rank {r}'s buffer: {lib.dls_last_error().decode()}")
+            self.ptrs.append(int(peer.value))
+        dist.barrier(group=ctx.control)
+
+    def local_tensor(self, dtype: torch.dtype, numel: int, byte_offset: int = 0) -> torch.Tensor:
+        itemsize = torch.empty(0, dtype=dtype).element_size()
+        assert byte_offset + numel * itemsize <= self.nbytes
+
+        class _Raw:
+            pass
+
+        raw = _Raw()
+        raw.__cuda_array_interface__ = {"shape": (numel * itemsize,), "typestr": "|u1",
+                                        "data": (self.local_ptr + byte_offset, False), "version": 2}
+        raw._keepalive = self
+        t = torch.as_tensor(raw, device=self.ctx.device)
+        return t.view(dtype)
+
+    def ptr(self, rank: int, byte_offset: int = 0) -> int:
+        return self.ptrs[rank] + byte_offset
+
+
+class ArenaPayload(dict):
+    """Message payload that lives in a rank's upload arena.  ``ptr`` is valid in THIS
+    process (local or peer-mapped); ``local`` is a tensor view when the row is ours."""
+
+    def __init__(self, rank: int, slot: int, ptr: int, layout: ParameterLayout, local: torch.Tensor | None) -> None:
+        super().__init__()
+        self.rank, self.slot, self.ptr, self.layout, self.local = rank, slot, ptr, layout, local
+
+    def to_local(self, ctx: "DistributedContext") -> FlatParameter:
+        if self.local is not None:
+            return FlatParameter(self.local.clone(), self.layout)
+        out = torch.empty(self.layout.total, dtype=torch.float32, device=ctx.device)
+        runtime.call("dls_copy_device", out.data_ptr(), self.ptr, self.layout.total * 4, runtime.stream_ptr(ctx.device))
+        ctx.peer_reads_pending = True
+        return FlatParameter(out, self.layout)
+
+
+class DistributedContext:
+    def __init__(self) -> None:
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        use_cuda = torch.cuda.is_available() and os.environ.get("DLS_FORCE_CPU", "0") != "1"
+        self.device = torch.device("cuda", self.local_rank) if use_cuda else torch.device("cpu")
+        if use_cuda:
+            torch.cuda.set_device(self.device)
+        if not dist.is_initialized():
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            if use_cuda:
+                dist.init_process_group("nccl", device_id=self.device)
+            else:
+                dist.init_process_group("gloo")
+        self.control = dist.new_group(backend="gloo") if dist.get_backend() != "gloo" else dist.group.WORLD
+        self.use_p2p = use_cuda and runtime.available() and os.environ.get("DLS_DISABLE_P2P", "0") != "1"
+        self.layout: ParameterLayout | None = None
+        self.arena: SymmetricBuffer | None = None
+        self.globals: SymmetricBuffer | None = None
+        self.flags: SymmetricBuffer | None = None
+        self.slots = 0
+        self.epoch = 0
+        self.global_index = 0
+        self.peer_reads_pending = False
+        self._flag_table: torch.Tensor | None = None
+        self.p2p_reductions = 0
+        get_logger().debug("rank %s/%s on %s, p2p=%s", self.rank, self.world, self.device, self.use_p2p)
+
+    # ---- ownership --------------------------------------------------------------------
+    def owner_of(self, worker_id: int) -> int:
+        return worker_id % self.world
+
+    def is_local(self, worker_id: int) -> bool:
+        return self.owner_of(worker_id) == self.rank
+
+    def slot_of(self, worker_id: int) -> int:
+        return worker_id // self.world
+
+    # ---- symmetric memory -----------------------------------------------------------------
+    def setup_arena(self, layout: ParameterLayout, worker_number: int) -> None:
+        """Collective.  One upload row per local worker, two global-model buffers, flag words."""
+        if not self.use_p2p:
+            return
+        if self.layout is not None and self.layout == layout and self.slots >= -(-worker_number // self.world):
+            return
+        self.layout = layout
+        self.slots = -(-worker_number // self.world)
+        self.row_bytes = ((layout.total * 4 + 255) // 256) * 256
+        self.arena = SymmetricBuffer(self, self.row_bytes * self.slots)
+        self.globals = SymmetricBuffer(self, self.row_bytes * 2)
+        self.flags = SymmetricBuffer(self, 256)
+        self._flag_table = runtime.pointer_table(self.flags.ptrs, self.device)
+        self._nan = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.epoch = 0
+
+    def arena_row(self, slot: int) -> torch.Tensor:
+        assert self.arena is not None and self.layout is not None
+        return self.arena.local_tensor(torch.float32, self.layout.total, slot * self.row_bytes)
+
+    def store_upload(self, worker_id: int, flat: torch.Tensor) -> ArenaPayload:
+        slot = self.slot_of(worker_id)
+        row = self.arena_row(slot)
+        row.copy_(flat, non_blocking=True)
+        return ArenaPayload(self.rank, slot, self.arena.ptr(self.rank, slot * self.row_bytes), self.layout, row)
+
+    def remote_payload(self, rank: int, slot: int) -> ArenaPayload:
+        assert self.arena is not None and self.layout is not None
+        local = self.arena_row(slot) if rank == self.rank else None
+        return ArenaPayload(rank, slot, self.arena.ptr(rank, slot * self.row_bytes), self.layout, local)
+
+    # ---- the fused reduce-scatter + all-gather ------------------------------------------------
+    def p2p_reduce(self, payloads: list[ArenaPayload], weights: list[float], old: torch.Tensor | None,
+                   old_scale: float, inv_total: float) -> FlatParameter:
+        assert self.globals is not None and self.layout is not None and self.flags is not None
+        n = self.layout.total
+        self.global_index ^= 1
+        off = self.global_index * self.row_bytes
+        if old is not None and old.data_ptr() == self.globals.local_ptr + off:
+            raise RuntimeError("old model aliases the destination buffer")
+        chunk = ((-(-n // self.world)) + 3) // 4 * 4
+        lo, hi = min(self.rank * chunk, n), min((self.rank + 1) * chunk, n)
+        rows = runtime.pointer_table([p.ptr for p in payloads], self.device)
+        w = torch.tensor(weights, dtype=torch.float32).pin_memory().to(self.device, non_blocking=True)
+        dsts = (ctypes.c_void_p * self.world)(*[self.globals.ptr(r, off) for r in range(self.world)])
+        self.epoch += 1
+        self._nan.zero_()
+        runtime.call("dls_fedavg_reduce_f32", rows.data_ptr(), w.data_ptr(), len(payloads), runtime.ptr(old),
+                     float(old_scale), float(inv_total), dsts, self.world, lo, hi, self._flag_table.data_ptr(),
+                     self.world, self.rank, self.epoch, self._nan.data_ptr(), runtime.stream_ptr(self.device))
+        self.p2p_reductions += 1
+        verdict = self.flags.local_tensor(torch.int32, 32)[16:25].cpu().tolist()
+        if verdict[8]:
+            raise RuntimeError("peer barrier timed out inside fedavg_reduce (a rank is missing)")
+        assert not any(verdict[: self.world]), "NaN in aggregated parameters"
+        return FlatParameter(self.globals.local_tensor(torch.float32, n, off), self.layout)
+
+    # ---- small collectives -------------------------------------------------------------------
+    def all_reduce_sum(self, t: torch.Tensor) -> torch.Tensor:
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return t
+
+    def exchange(self, obj: Any) -> list[Any]:
+        out: list[Any] = [None] * self.world
+        dist.all_gather_object(out, obj, group=self.control)
+        return out
+
+    def fence(self) -> None:
+        """Everyone has finished reading everyone's arena rows (non-fused consumers)."""
+        if self.device.type == "cuda":
+            torch.cuda.current_stream(self.device).synchronize()
+        dist.barrier(group=self.control)
+        self.peer_reads_pending = False

@@ -1,9 +1,42 @@
+"""``train()`` under ``torch.distributed.run``: each rank runs its local workers and a
+server replica (see ``parallel/topology.py``)."""
 import os
+import threading
+from typing import Any
+
+import torch.distributed as dist
+
+from ..engine.log import add_file_handler, get_logger
+from ..engine.model_util import ModelUtil, ParameterLayout
+from .context import get_context, is_distributed  # noqa: F401
 
 
-def is_distributed() -> bool:
-    return int(os.environ.get("WORLD_SIZE", "1")) > 1 and os.environ.get("DLS_DISABLE_DISTRIBUTED", "0") != "1"
+def train_distributed(config: Any, practitioners: None | set, task_id: int | None) -> None:
+    from ..algorithm_factory import get_worker_config
+    from ..training import _Task, _last_results
 
-
-def train_distributed(config, practitioners, task_id):
-    raise NotImplementedError("filled in by the multi-GPU milestone")
+    ctx = get_context()
+    shared = [config.save_dir, config.log_file]
+    dist.broadcast_object_list(shared, src=0, group=ctx.control)
+    config.save_dir, config.log_file = shared
+    if config.log_file and ctx.rank == 0:
+        add_file_handler(config.log_file)
+    config.apply_global_config()
+    config.parallel_number = 1
+    if ctx.use_p2p:
+        dc = config.create_dataset_collection()
+        model = config._create_model(dc)
+        layout = ParameterLayout.from_dict(ModelUtil(model).get_parameter_dict())
+        ctx.setup_arena(layout, config.worker_number)
+    worker_config = get_worker_config(config, practitioners=practitioners)
+    task = _Task(task_id, config, worker_config)
+    threading.current_thread().name = f"rank {ctx.rank}"
+    task.start()
+    task.wait()
+    task.raise_errors()
+    _last_results.clear()
+    _last_results.update(task.results)
+    _last_results["save_dir"] = config.save_dir
+    dist.barrier(group=ctx.control)
+    get_logger().debug("rank %s finished", ctx.rank)
+    return None

@@ -31,6 +31,11 @@ class Server(Executor):
         name: str = "server"
         if task_id is not None:
             name = f"server of {task_id}"
+        from ..parallel import context as dist_context
+
+        self._dist = dist_context.get_context() if dist_context.is_distributed() else None
+        if self._dist is not None and self._dist.rank != 0:
+            name = f"{name} replica {self._dist.rank}"
         kwargs.setdefault("device_index", 0)
         super().__init__(**kwargs, name=name)
         self._endpoint: ServerEndpoint = endpoint
@@ -47,6 +52,9 @@ class Server(Executor):
         tester.dataset_collection.remove_dataset(phase=MachineLearningPhase.Training)
         tester.dataset_collection.remove_dataset(phase=MachineLearningPhase.Validation)
         tester.hook_config.summarize_executor = False
+        if self._dist is not None:
+            # every replica evaluates its shard of the test split; the sums are all-reduced
+            tester.shard(self._dist.rank, self._dist.world, self._dist)
         return tester
 
     def _load_into_tester(self, parameter_dict: TensorDict) -> None:
@@ -128,6 +136,9 @@ class Server(Executor):
 
     def _send_result(self, result: Message) -> None:
         self._before_send_result(result=result)
+        fence = getattr(self._endpoint.topology, "pre_send_fence", None)
+        if fence is not None:
+            fence()  # peers may still be reading this rank's upload rows
         if "worker_result" in result.other_data:
             for worker_id, data in result.other_data["worker_result"].items():
                 self._endpoint.send(worker_id=worker_id, data=data)

@@ -45,9 +45,13 @@ class _Task:
         server_config = worker_config.get("server")
         if server_config is not None:
             self.server = server_config["constructor"](extra_kwargs=dict(extra), extra_endpoint_kwargs=dict(extra_ep))
+        is_local = getattr(self.topology, "is_local", lambda worker_id: True)
         for group in worker_config["worker"].values():
             for wc in group:
-                self.workers.append(wc["constructor"](extra_kwargs=dict(extra), extra_endpoint_kwargs=dict(extra_ep)))
+                worker_id = wc["constructor"].keywords["endpoint_kwargs"]["worker_id"]
+                if is_local(worker_id):
+                    self.workers.append(wc["constructor"](extra_kwargs=dict(extra),
+                                                          extra_endpoint_kwargs=dict(extra_ep)))
 
     def _run(self, role: Any, is_server: bool) -> None:
         try:
@@ -125,6 +129,7 @@ def train(config: Any, practitioners: None | set = None) -> int | None:
     task.raise_errors()
     _last_results.clear()
     _last_results.update(task.results)
+    _last_results["save_dir"] = config.save_dir
     get_logger().info("training use %s seconds", timer.elapsed_milliseconds() / 1000)
     return None
 

@@ -60,6 +60,7 @@ int dls_ipc_get_handle(void* ptr, unsigned char* handle_out64);   /* cudaIpcGetM
 int dls_ipc_open_handle(const unsigned char* handle64, void** out_ptr);
 int dls_ipc_close_handle(void* ptr);
 int dls_enable_peer_access(int device, int peer);
+int dls_copy_device(void* dst, const void* src, long long bytes, void* stream); /* src may be peer-mapped */
 
 /* ---- local SGD (reference: external torch.optim.SGD inside Trainer.train(), and
  *      simulation_lib/worker/gradient_worker.py:13-26,96-116) --------------------------

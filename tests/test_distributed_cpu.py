@@ -1,0 +1,65 @@
+"""One process per "GPU" with the gloo backend on CPU, world_size 2: server replicas must
+agree with each other and with the single-process run (same seed => same decisions)."""
+import json
+import os
+import socket
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+SCRIPT = r"""
+import json, os, sys
+sys.path.insert(0, {root!r})
+from distributed_learning_simulator_b200 import load_config_from_dict, train
+from distributed_learning_simulator_b200.training import get_last_training_result
+conf = {conf!r}
+config = load_config_from_dict(conf)
+train(config)
+res = get_last_training_result()
+out = os.path.join({out!r}, "rank_%s.json" % os.environ.get("RANK", "0"))
+with open(out, "w") as f:
+    json.dump({{"performance": {{str(k): v for k, v in res["performance"].items()}}, "save_dir": res["save_dir"]}}, f)
+"""
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _run(tmp_path, conf, world):
+    out = tmp_path / f"world{world}"
+    out.mkdir()
+    script = tmp_path / f"run{world}.py"
+    script.write_text(SCRIPT.format(root=ROOT, conf=conf, out=str(out)))
+    env = dict(os.environ, DLS_FORCE_CPU="1", DLS_OUTPUT_ROOT=str(out), OMP_NUM_THREADS="2")
+    if world == 1:
+        cmd = [sys.executable, str(script)]
+        env.pop("WORLD_SIZE", None)
+    else:
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+               "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), str(script)]
+    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    return [json.load(open(out / f"rank_{r}.json")) for r in range(world)]
+
+
+def test_two_ranks_agree_with_single_process(tmp_path):
+    conf = {"dataset_name": "MNIST", "model_name": "LeNet5", "distributed_algorithm": "fed_avg",
+            "optimizer_name": "SGD", "learning_rate_scheduler_name": "CosineAnnealingLR", "worker_number": 4,
+            "batch_size": 32, "round": 2, "epoch": 1, "learning_rate": 0.05,
+            "algorithm_kwargs": {"random_client_number": 3},
+            "dataset_kwargs": {"train_size": 640, "test_size": 200}}
+    two = _run(tmp_path, conf, 2)
+    one = _run(tmp_path, conf, 1)
+    assert two[0]["performance"] == two[1]["performance"]
+    assert two[0]["save_dir"] == two[1]["save_dir"]
+    assert sorted(two[0]["performance"]) == ["1", "2"]
+    for k in ("1", "2"):
+        a, b = two[0]["performance"][k], one[0]["performance"][k]
+        assert abs(a["test_accuracy"] - b["test_accuracy"]) < 1e-4
+        assert abs(a["test_loss"] - b["test_loss"]) < 1e-4
+    server_dir = os.path.join(two[0]["save_dir"], "server")
+    assert os.path.isfile(os.path.join(server_dir, "round_record.json"))

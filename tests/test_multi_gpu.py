@@ -1,0 +1,92 @@
+"""Two ranks, two GPUs: the peer-mapped arena + fused P2P reduce/broadcast kernel against a
+plain fp64 PyTorch reduction, then a short federated run through the public API.
+Skipped unless two CUDA devices are visible (run with ``gpurun --gpus 2``)."""
+import json
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+SCRIPT = r"""
+import json, os, sys
+sys.path.insert(0, {root!r})
+import torch
+from distributed_learning_simulator_b200.parallel.context import get_context
+from distributed_learning_simulator_b200.engine.model_util import ParameterLayout
+
+ctx = get_context()
+assert ctx.use_p2p
+numels = [1728, 64, 36864, 10, 7, 5120, 33, 4099, 1000003]
+layout = ParameterLayout([f"t{{i}}" for i in range(len(numels))], [torch.Size([n]) for n in numels])
+ctx.setup_arena(layout, worker_number=2 * ctx.world + 1)
+n = layout.total
+errs = []
+old = torch.randn(n, device=ctx.device, generator=torch.Generator(device="cuda").manual_seed(1))
+for rnd in range(3):
+    payloads, rows, weights = [], [], []
+    n_workers = 2 * ctx.world + 1
+    for w in range(n_workers):
+        g = torch.Generator(device="cuda").manual_seed(100 * rnd + w)
+        row = torch.randn(n, device=ctx.device, generator=g)   # every rank can recompute every row
+        rows.append(row)
+        weights.append(float(10 + w))
+        if ctx.is_local(w):
+            ctx.store_upload(w, row)
+    torch.cuda.synchronize()
+    for w in range(n_workers):
+        payloads.append(ctx.remote_payload(ctx.owner_of(w), ctx.slot_of(w)))
+    out = ctx.p2p_reduce(payloads, weights, old, 1.0, 1.0 / sum(weights)).flat
+    ref = old.double()
+    for r, wt in zip(rows, weights):
+        ref = ref + r.double() * (wt / sum(weights))
+    errs.append(float((out.double() - ref).abs().max()))
+    old = out.clone()
+with open(os.path.join({out!r}, "p2p_%d.json" % ctx.rank), "w") as f:
+    json.dump({{"errs": errs, "reductions": ctx.p2p_reductions}}, f)
+
+from distributed_learning_simulator_b200 import load_config_from_dict, train
+from distributed_learning_simulator_b200.training import get_last_training_result
+conf = {{"dataset_name": "MNIST", "model_name": "LeNet5", "distributed_algorithm": "fed_avg",
+        "optimizer_name": "SGD", "learning_rate_scheduler_name": "CosineAnnealingLR", "worker_number": 4,
+        "batch_size": 32, "round": 3, "epoch": 1, "learning_rate": 0.1, "log_level": "WARNING",
+        "dataset_kwargs": {{"train_size": 1280, "test_size": 400}}}}
+before = ctx.p2p_reductions
+train(load_config_from_dict(conf))
+res = get_last_training_result()
+with open(os.path.join({out!r}, "train_%d.json" % ctx.rank), "w") as f:
+    json.dump({{"performance": {{str(k): v for k, v in res["performance"].items()}},
+               "p2p_reductions": ctx.p2p_reductions - before}}, f)
+"""
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_p2p_reduce_and_distributed_training(tmp_path):
+    world = 2
+    script = tmp_path / "run.py"
+    script.write_text(SCRIPT.format(root=ROOT, out=str(tmp_path)))
+    env = dict(os.environ, DLS_OUTPUT_ROOT=str(tmp_path))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), str(script)]
+    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    for r in range(world):
+        p2p = json.load(open(tmp_path / f"p2p_{r}.json"))
+        assert max(p2p["errs"]) < 1e-5, p2p
+        assert p2p["reductions"] == 3
+    t0, t1 = (json.load(open(tmp_path / f"train_{r}.json")) for r in range(world))
+    assert t0["performance"] == t1["performance"]
+    assert t0["p2p_reductions"] == 3 and t1["p2p_reductions"] == 3
+    assert t0["performance"]["3"]["test_accuracy"] > 0.2
