@@ -85,6 +85,11 @@ class FlatParameter(dict):
     def __reduce__(self):  # pickles as a plain dict of CPU-able tensors
         return (dict, (dict(self),))
 
+    def __copy__(self):  # a shallow copy stays flat (``copy.copy`` would otherwise go through __reduce__)
+        if self.is_intact():
+            return FlatParameter(self.flat, self.layout)
+        return dict(self)
+
 
 def as_flat(parameter: TensorDict) -> "FlatParameter | None":
     if isinstance(parameter, FlatParameter) and parameter.is_intact():

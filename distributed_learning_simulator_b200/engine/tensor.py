@@ -30,6 +30,28 @@ def recursive_tensor_op(data: Any, fun: Callable, **kwargs: Any) -> Any:
     return data
 
 
+def for_each_tensor(data: Any, fun: Callable) -> None:
+    """Visit every tensor without rebuilding (or replacing) any container."""
+    if isinstance(data, torch.Tensor):
+        fun(data)
+    elif isinstance(data, dict):
+        flat = getattr(data, "flat", None)
+        if isinstance(flat, torch.Tensor):
+            fun(flat)  # flat payloads: the views share this storage
+        else:
+            for v in data.values():
+                for_each_tensor(v, fun)
+        extra = getattr(data, "partial_flat", None)
+        if isinstance(extra, torch.Tensor):
+            fun(extra)
+    elif isinstance(data, (list, tuple, set)):
+        for v in data:
+            for_each_tensor(v, fun)
+    elif dataclasses.is_dataclass(data) and not isinstance(data, type):
+        for f in dataclasses.fields(data):
+            for_each_tensor(getattr(data, f.name), fun)
+
+
 def tensor_to(data: Any, non_blocking: bool = True, **kwargs: Any) -> Any:
     def fun(t: torch.Tensor, **kw: Any) -> torch.Tensor:
         return t.to(non_blocking=non_blocking, **kw)

@@ -18,7 +18,7 @@ from typing import Any
 import torch
 
 from .engine.model_util import FlatParameter, ParameterLayout, as_flat  # noqa: F401
-from .engine.tensor import TensorDict, recursive_tensor_op
+from .engine.tensor import TensorDict, for_each_tensor
 
 
 @dataclass(kw_only=True)
@@ -69,13 +69,12 @@ def get_message_size(msg: Any) -> int:
     cnt: int = 0
     seen: set[int] = set()
 
-    def count(data: torch.Tensor, **kwargs: Any) -> torch.Tensor:
+    def count(data: torch.Tensor) -> None:
         nonlocal cnt
         if id(data) not in seen:
             seen.add(id(data))
             cnt += data.element_size() * data.numel()
-        return data
 
-    recursive_tensor_op(msg, fun=count)
+    for_each_tensor(msg, count)
     assert cnt > 0
     return cnt

@@ -15,6 +15,8 @@ from ..engine.model_util import FlatParameter, ParameterLayout, as_flat
 from . import runtime
 
 _group_cache: dict[tuple, tuple[torch.Tensor, torch.Tensor]] = {}
+# how many aggregations each fused path has served in this process (tests and bench read it)
+STATS = {"f32": 0, "packed": 0, "p2p": 0}
 
 
 def layout_tables(layout: ParameterLayout, device: torch.device) -> tuple[torch.Tensor, torch.Tensor]:
@@ -137,6 +139,7 @@ def reduce_rows_f32(rows: list[torch.Tensor], weights: list[float], old: torch.T
     runtime.call("dls_fedavg_reduce_f32", row_table.data_ptr(), w.data_ptr(), len(rows), runtime.ptr(old),
                  float(old_scale), float(inv_total), dst_table, 1, 0, n, None, 1, 0, 0, flag.data_ptr(),
                  runtime.stream_ptr(device))
+    STATS["f32"] += 1
     if check_nan:
         _nan_check(flag)
     return out
@@ -152,6 +155,7 @@ def fused_aggregate(pending: dict, old_parameter_dict: Any, variant: str) -> Fla
         from ..parallel import context as dist_context
 
         is_delta = payloads[0][1]
+        STATS["p2p"] += 1
         return dist_context.get_context().p2p_reduce(
             [p for p, _ in payloads], weights, old.flat if (is_delta and old is not None) else None,
             1.0 if is_delta else 0.0, 1.0 / total)
@@ -211,6 +215,7 @@ def _packed_aggregate(msgs: list, payloads: list, weights: list[float], old: Fla
     runtime.call("dls_fedavg_reduce_packed", dev_rows.data_ptr(), len(msgs), runtime.ptr(old.flat) if old else None,
                  t_off.data_ptr(), g_off.data_ptr(), len(layout.names), int(variant == "dropout"), out.data_ptr(),
                  flag.data_ptr(), runtime.stream_ptr(device))
+    STATS["packed"] += 1
     _nan_check(flag)
     del keep
     return FlatParameter(out, layout)

@@ -22,7 +22,7 @@ from typing import Any
 
 import torch
 
-from ..engine.tensor import recursive_tensor_op
+from ..engine.tensor import for_each_tensor, recursive_tensor_op
 
 
 class TopologyClosed(RuntimeError):
@@ -46,24 +46,22 @@ class _Envelope:
             stream = torch.cuda.current_stream()
             stream.wait_event(self.event)
 
-            def keep(t: torch.Tensor) -> torch.Tensor:
+            def keep(t: torch.Tensor) -> None:
                 if t.is_cuda:
                     t.record_stream(stream)
-                return t
 
-            recursive_tensor_op(self.data, keep)
+            for_each_tensor(self.data, keep)
         return self.data
 
 
 def _has_cuda_tensor(data: Any) -> bool:
     found = False
 
-    def probe(t: torch.Tensor) -> torch.Tensor:
+    def probe(t: torch.Tensor) -> None:
         nonlocal found
         found = found or t.is_cuda
-        return t
 
-    recursive_tensor_op(data, probe)
+    for_each_tensor(data, probe)
     return found
 
 
@@ -74,9 +72,8 @@ def _shallow_message_copy(data: Any) -> Any:
     new = copy.copy(data)
     for name in data.__dataclass_fields__:
         v = getattr(data, name)
-        if isinstance(v, dict):
-            c = copy.copy(v)
-            setattr(new, name, c)
+        if type(v) is dict:  # plain dicts (other_data); flat / arena payloads are shared as they are
+            setattr(new, name, dict(v))
     return new
 
 

@@ -16,27 +16,24 @@ def _conf(**kw):
 
 
 def test_graph_step_matches_eager():
-    """Same data order, same init: captured step == eager torch.optim.SGD step."""
-    from distributed_learning_simulator_b200 import load_config_from_dict
-    from distributed_learning_simulator_b200.engine.ml_type import MachineLearningPhase
+    """Same data order, same init: the captured step (fused multi-tensor SGD, device-side LR
+    schedule, remainder batch) reproduces the eager torch.optim.SGD loop.  Runs in a fresh
+    process (tools/check_graph_step.py) with TF32 off."""
+    import json
+    import os
+    import subprocess
+    import sys
 
-    torch.backends.cudnn.allow_tf32 = False
-    torch.backends.cuda.matmul.allow_tf32 = False
-    finals = []
-    for use_graph in (True, False):
-        config = load_config_from_dict(_conf(use_cuda_graph=use_graph))
-        trainer = config.create_trainer()
-        trainer.dataset_collection.remove_dataset(MachineLearningPhase.Validation)
-        trainer.set_seed(123)
-        trainer.set_device(torch.device("cuda", 0))
-        trainer.train()
-        trainer.wait_stream()
-        finals.append(trainer.model_util.get_parameter_list().clone())
-        m = trainer.performance_metric.get_epoch_metrics(2)
-        assert 0 <= m["accuracy"] <= 1
-        if use_graph:
-            assert trainer._graph_step is not None and trainer._graph_step.replays == 2 * 22
-    torch.testing.assert_close(finals[0], finals[1], rtol=2e-4, atol=2e-5)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    res = subprocess.run([sys.executable, os.path.join(root, "tools", "check_graph_step.py")], capture_output=True,
+                         text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
+    out = json.loads(res.stdout.strip().splitlines()[-1])
+    assert out["replays"]["g1"] == 2 * 22 and out["replays"]["e1"] == 0
+    assert max(out["diffs"].values()) < 1e-5, out["diffs"]
+    for e in range(2):
+        assert abs(out["metrics"]["g1"][e]["loss"] - out["metrics"]["e1"][e]["loss"]) < 1e-5
+        assert abs(out["metrics"]["g1"][e]["accuracy"] - out["metrics"]["e1"][e]["accuracy"]) < 1e-6
 
 
 def test_fed_avg_on_gpu_uses_fused_paths():
@@ -44,13 +41,19 @@ def test_fed_avg_on_gpu_uses_fused_paths():
     from distributed_learning_simulator_b200.ops import runtime
     from distributed_learning_simulator_b200.training import get_last_training_result
 
+    from distributed_learning_simulator_b200.engine import graph_step
+    from distributed_learning_simulator_b200.ops import reduce as R
+
     before = runtime.launch_count()
+    fused_before, replay_before = R.STATS["f32"], graph_step.REPLAY_COUNTER[0]
     config = load_config_from_dict(_conf(worker_number=3, learning_rate=0.1))
     train(config)
     perf = get_last_training_result()["performance"]
     assert sorted(perf) == [1, 2]
     assert perf[2]["test_accuracy"] > 0.15
     assert runtime.launch_count() > before
+    assert R.STATS["f32"] - fused_before == 2, "each round must be aggregated by the fused kernel"
+    assert graph_step.REPLAY_COUNTER[0] > replay_before, "local training must run as CUDA-graph replays"
 
 
 def test_smoke_entry():

@@ -1,0 +1,64 @@
+"""Messages, flat payloads, topology hand-off."""
+import copy
+import threading
+
+import torch
+
+from distributed_learning_simulator_b200.engine.model_util import FlatParameter, ParameterLayout, as_flat
+from distributed_learning_simulator_b200.message import (DeltaParameterMessage, Message, ParameterMessage,
+                                                          get_message_size)
+from distributed_learning_simulator_b200.topology import ClientEndpoint, ServerEndpoint, ThreadCentralTopology
+
+
+def _flat():
+    layout = ParameterLayout(["a", "b"], [torch.Size([2, 3]), torch.Size([4])])
+    return FlatParameter(torch.arange(10, dtype=torch.float32), layout)
+
+
+def test_messages_and_restore():
+    old = {"a": torch.ones(2), "b": torch.zeros(3)}
+    d = DeltaParameterMessage(dataset_size=5, delta_parameter={"a": torch.full((2,), 2.0)}, other_data={"x": 1},
+                              in_round=True)
+    msg = d.restore(old)
+    assert isinstance(msg, ParameterMessage) and msg.dataset_size == 5 and msg.in_round and msg.other_data == {"x": 1}
+    assert torch.equal(msg.parameter["a"], torch.full((2,), 3.0)) and torch.equal(msg.parameter["b"], old["b"])
+    assert torch.equal(old["a"], torch.ones(2))  # not modified in place
+    p = ParameterMessage(parameter={"a": torch.ones(2)})
+    p.complete(old)
+    assert set(p.parameter) == {"a", "b"}
+    assert get_message_size(p) == 4 * 5
+    assert get_message_size(ParameterMessage(parameter=_flat())) == 40
+    assert Message().other_data == {} and not Message().end_training
+
+
+def test_flat_parameter_survives_shallow_copy_and_handoff():
+    fp = _flat()
+    assert as_flat(fp) is fp and fp["a"].shape == (2, 3)
+    assert as_flat(copy.copy(fp)) is not None
+    fp2 = _flat()
+    fp2["a"] = torch.zeros(2, 3)
+    assert as_flat(fp2) is None  # an entry was replaced: only the dict view is valid
+    topo = ThreadCentralTopology(2)
+    server, c0, c1 = ServerEndpoint(topo), ClientEndpoint(topo, 0), ClientEndpoint(topo, 1)
+    msg = ParameterMessage(parameter=fp, other_data={"k": 1})
+    server.broadcast(msg, worker_ids={0, 1})
+    got0, got1 = c0.get(), c1.get()
+    assert as_flat(got0.parameter) is not None and as_flat(got1.parameter) is not None
+    assert got0 is not got1 and got0.other_data is not got1.other_data
+    assert got0.parameter.flat.data_ptr() == fp.flat.data_ptr()  # zero-copy hand-off
+    c1.send(None)
+    c0.send(DeltaParameterMessage(dataset_size=1, delta_parameter=fp))
+    assert server.wait_for_data({0, 1}, timeout=1.0) == {0, 1}
+    assert server.get(1) is None
+    assert as_flat(server.get(0).delta_parameter) is not None
+    assert server.wait_for_data({0}, timeout=0.05) == set()
+
+
+def test_event_driven_wait_wakes_up():
+    topo = ThreadCentralTopology(1)
+    server, client = ServerEndpoint(topo), ClientEndpoint(topo, 0)
+    t = threading.Timer(0.05, lambda: client.send(Message(other_data={"hello": True})))
+    t.start()
+    assert server.wait_for_data({0}, timeout=5.0) == {0}
+    assert server.get(0).other_data["hello"]
+    assert not client.has_data() and not client.wait_for_data(timeout=0.01)
