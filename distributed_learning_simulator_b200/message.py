@@ -53,8 +53,13 @@ class DeltaParameterMessage(ParameterMessageBase):
     delta_parameter: TensorDict
 
     def restore(self, parameter: TensorDict) -> ParameterMessage:
-        new_parameter = {}
-        for k, v in parameter.items():
+        old_flat, delta_flat = as_flat(parameter), as_flat(self.delta_parameter)
+        if old_flat is not None and delta_flat is not None and old_flat.layout == delta_flat.layout:
+            new_parameter: TensorDict = FlatParameter(
+                old_flat.flat + delta_flat.flat.to(old_flat.flat.device), old_flat.layout)
+        else:
+            new_parameter = {}
+        for k, v in ([] if new_parameter else parameter.items()):
             d = self.delta_parameter.get(k)
             new_parameter[k] = v + d.to(v.device) if d is not None else v
         msg = ParameterMessage(parameter=new_parameter)
