@@ -46,15 +46,19 @@ class GraphNodeEmbeddingPassingAlgorithm(FedAVGAlgorithm):
                     for worker_id, data in self._all_worker_data.items()}})
             res: dict = {"worker_result": {}}
             if self.__embeddings:
-                table = torch.cat(self.__embeddings)
-                ids = torch.cat(self.__embedding_ids)
+                device = self.__embeddings[0].device
+                table = torch.cat([e.to(device) for e in self.__embeddings])
+                ids = torch.cat([i.to(device) for i in self.__embedding_ids])
                 order = torch.argsort(ids)
                 sorted_ids = ids[order]
             for worker_id, boundary in self.__boundaries.items():
                 node_indices: tuple = ()
                 node_embedding = None
-                if self.__embeddings and boundary:
-                    want = torch.as_tensor(sorted(boundary), dtype=torch.long, device=sorted_ids.device)
+                if self.__embeddings and len(boundary):
+                    if isinstance(boundary, torch.Tensor):
+                        want = torch.unique(boundary.to(sorted_ids.device))
+                    else:
+                        want = torch.as_tensor(sorted(boundary), dtype=torch.long, device=sorted_ids.device)
                     pos = torch.searchsorted(sorted_ids, want).clamp(max=sorted_ids.numel() - 1)
                     hit = sorted_ids[pos] == want
                     if bool(hit.any()):

@@ -23,9 +23,10 @@ from typing import Any
 import yaml
 
 from .engine.config import Config
-from .engine.dataset import ClassificationDatasetCollection, get_dataset_collection_sampler
+from .engine.dataset import ClassificationDatasetCollection
 from .engine.device import get_devices
 from .practitioner import Practitioner
+from .sampler import get_dataset_collection_sampler
 
 CONF_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "conf")
 
