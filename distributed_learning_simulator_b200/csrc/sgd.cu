@@ -86,8 +86,8 @@ __global__ void sgd_tick_kernel(int32_t* state) {
 __global__ void __launch_bounds__(256)
 gather_batch_kernel(const float* __restrict__ x_all, const long long* __restrict__ y_all,
                     const long long* __restrict__ order, long long n_order, const int32_t* __restrict__ state,
-                    int state_index, int batch_stride, long long row_elems, float* __restrict__ x_out,
-                    long long* __restrict__ y_out) {
+                    int state_index, int batch_stride, long long row_elems, int channels,
+                    float* __restrict__ x_out, long long* __restrict__ y_out) {
     const int b = blockIdx.x;
     // batch_stride is the epoch's regular batch size: the (smaller) last batch starts at
     // index * stride too
@@ -96,7 +96,15 @@ gather_batch_kernel(const float* __restrict__ x_all, const long long* __restrict
     const long long src = order[pos];
     const float* in = x_all + src * row_elems;
     float* out = x_out + (long long)b * row_elems;
-    if ((row_elems & 3) == 0) {
+    if (channels > 1) {
+        // source rows are C,H,W; the model runs channels-last, so emit H,W,C
+        const long long hw = row_elems / channels;
+        for (long long v = threadIdx.x; v < row_elems; v += blockDim.x) {
+            const long long pix = v / channels;
+            const int c = (int)(v - pix * channels);
+            out[v] = in[(long long)c * hw + pix];
+        }
+    } else if ((row_elems & 3) == 0) {
         const long long nv = row_elems >> 2;
         for (long long v = threadIdx.x; v < nv; v += blockDim.x)
             reinterpret_cast<float4*>(out)[v] = ld_stream_f4(in + (v << 2));
@@ -172,11 +180,13 @@ extern "C" int dls_sgd_tick(int32_t* state, void* stream) {
 
 extern "C" int dls_gather_batch(const float* x_all, const long long* y_all, const long long* order,
                                 long long n_order, const int32_t* state, int state_index, int batch,
-                                int batch_stride, long long row_elems, float* x_out, long long* y_out,
-                                void* stream) {
+                                int batch_stride, long long row_elems, int nhwc_channels, float* x_out,
+                                long long* y_out, void* stream) {
     if (batch < 1 || n_order < 1 || batch_stride < batch) return fail_msg("dls_gather_batch: bad batch/order");
+    if (nhwc_channels > 1 && row_elems % nhwc_channels) return fail_msg("dls_gather_batch: bad channel count");
     gather_batch_kernel<<<batch, 256, 0, (cudaStream_t)stream>>>(x_all, y_all, order, n_order, state, state_index,
-                                                                 batch_stride, row_elems, x_out, y_out);
+                                                                 batch_stride, row_elems, nhwc_channels, x_out,
+                                                                 y_out);
     DLS_LAUNCHED("gather_batch_kernel");
     return 0;
 }

@@ -13,6 +13,7 @@ The reference's counterpart is the external ``Trainer.train()`` eager loop with
 ``torch.optim.SGD`` (one ATen launch per tensor per step) invoked at
 /root/reference/simulation_lib/worker/worker.py:86-88.
 """
+import os
 import threading
 import time
 from typing import Any
@@ -35,6 +36,11 @@ H2D_BYTES = [0]
 KERNELS_PER_REPLAY = 4  # gather_batch, sgd_step, sgd_tick, metric_accumulate
 
 
+def _same_physical_layout(a: torch.Tensor, b: torch.Tensor) -> bool:
+    """Equal strides on every dimension that has more than one element."""
+    return a.shape == b.shape and all(sa == sb for n, sa, sb in zip(a.shape, a.stride(), b.stride()) if n > 1)
+
+
 class _CapturedStep:
     def __init__(self) -> None:
         self.graph: torch.cuda.CUDAGraph | None = None
@@ -47,6 +53,8 @@ class _CapturedStep:
 class GraphTrainStep:
     def __init__(self, trainer: Any) -> None:
         runtime.require()
+        if os.environ.get("DLS_CUDNN_BENCHMARK", "1") != "0":
+            torch.backends.cudnn.benchmark = True  # shapes are static: let cuDNN pick its fastest kernels
         self.trainer = trainer
         self.device = trainer.device
         self.util = trainer.model_util
@@ -101,8 +109,10 @@ class GraphTrainStep:
         params = list(self.trainer.model.parameters())
         step.grads = [p.grad for p in params]
         ptrs = [0 if g is None else g.data_ptr() for g in step.grads]
-        for g in step.grads:
-            assert g is None or (g.dtype == torch.float32 and g.is_contiguous())
+        for p, g in zip(params, step.grads):
+            # the fused update walks physical memory: a gradient must be laid out like its parameter
+            # (autograd's layout contract gives channels-last grads for channels-last weights)
+            assert g is None or (g.dtype == torch.float32 and _same_physical_layout(g, p)), (g.stride(), p.stride())
         step.grad_table.copy_(torch.tensor(ptrs, dtype=torch.int64))
 
     def _capture(self, batch: int, x_all: torch.Tensor, y_all: torch.Tensor, n_order: int) -> _CapturedStep:
@@ -114,6 +124,8 @@ class GraphTrainStep:
         assert self.trainer.hyper_parameter.optimizer_name.lower() == "sgd", "the fused step implements SGD"
         step = _CapturedStep()
         step.x = torch.empty((batch, *x_all.shape[1:]), dtype=x_all.dtype, device=self.device)
+        if step.x.dim() == 4 and step.x.shape[1] > 1 and any(f for f in self.layout.formats):
+            step.x = step.x.contiguous(memory_format=torch.channels_last)  # match the channels-last weights
         step.y = torch.empty(batch, dtype=torch.int64, device=self.device)
         params = list(t.model.parameters())
         # warm-up (lazy init, cuDNN heuristics) must not change the training state

@@ -10,6 +10,7 @@ gradient) as a view into ONE contiguous fp32 buffer.  Every communication hot pa
 1-D kernel over ``[P]`` with a per-tensor segment table, and a worker upload is a
 ``[P]`` row of a device arena instead of a pickled dict of CPU tensors.
 """
+import os
 from typing import Any, Iterable
 
 import torch
@@ -18,12 +19,20 @@ from torch import nn
 from .tensor import TensorDict
 
 
-class ParameterLayout:
-    """Segment table of a flat parameter vector: names, shapes, offsets."""
+def _is_channels_last(t: torch.Tensor) -> bool:
+    """4-D tensor physically stored as N,H,W,C (and not also plain-contiguous)."""
+    return t.dim() == 4 and not t.is_contiguous() and t.is_contiguous(memory_format=torch.channels_last)
 
-    def __init__(self, names: list[str], shapes: list[torch.Size]) -> None:
+
+class ParameterLayout:
+    """Segment table of a flat parameter vector: names, shapes, offsets, and which 4-D
+    tensors are stored channels-last (N,H,W,C order inside their segment) so that cuDNN's
+    tensor-core convolutions need no layout conversion kernels."""
+
+    def __init__(self, names: list[str], shapes: list[torch.Size], formats: list[int] | None = None) -> None:
         self.names = list(names)
         self.shapes = [torch.Size(s) for s in shapes]
+        self.formats = list(formats) if formats is not None else [0] * len(self.names)
         self.numels = [int(s.numel()) for s in self.shapes]
         self.offsets = [0]
         for n in self.numels:
@@ -33,31 +42,38 @@ class ParameterLayout:
 
     @classmethod
     def from_dict(cls, parameter_dict: TensorDict) -> "ParameterLayout":
-        return cls(list(parameter_dict.keys()), [v.shape for v in parameter_dict.values()])
+        return cls(list(parameter_dict.keys()), [v.shape for v in parameter_dict.values()],
+                   [int(_is_channels_last(v)) for v in parameter_dict.values()])
 
     def __eq__(self, other: object) -> bool:
-        return isinstance(other, ParameterLayout) and self.names == other.names and self.shapes == other.shapes
+        return isinstance(other, ParameterLayout) and self.names == other.names and self.shapes == other.shapes \
+            and self.formats == other.formats
 
     def __hash__(self) -> int:
-        return hash((tuple(self.names), tuple(tuple(s) for s in self.shapes)))
+        return hash((tuple(self.names), tuple(tuple(s) for s in self.shapes), tuple(self.formats)))
 
     def slice_of(self, name: str) -> slice:
         i = self.index[name]
         return slice(self.offsets[i], self.offsets[i + 1])
 
+    def view_of(self, flat: torch.Tensor, i: int) -> torch.Tensor:
+        seg = flat[self.offsets[i] : self.offsets[i + 1]]
+        shape = self.shapes[i]
+        if self.formats[i]:
+            o, c, h, w = shape
+            return seg.view(o, h, w, c).permute(0, 3, 1, 2)
+        return seg.view(shape)
+
     def views(self, flat: torch.Tensor) -> TensorDict:
         assert flat.numel() == self.total
-        return {
-            n: flat[self.offsets[i] : self.offsets[i + 1]].view(self.shapes[i])
-            for i, n in enumerate(self.names)
-        }
+        return {n: self.view_of(flat, i) for i, n in enumerate(self.names)}
 
     def flatten(self, parameter_dict: TensorDict, out: torch.Tensor | None = None) -> torch.Tensor:
         if out is None:
             ref = next(iter(parameter_dict.values()))
             out = torch.empty(self.total, dtype=torch.float32, device=ref.device)
         for i, n in enumerate(self.names):
-            out[self.offsets[i] : self.offsets[i + 1]].copy_(parameter_dict[n].reshape(-1))
+            self.view_of(out, i).copy_(parameter_dict[n])
         return out
 
     def segment_offsets(self, device: torch.device | str = "cpu") -> torch.Tensor:
@@ -146,13 +162,16 @@ class ModelUtil:
                 off += n
 
     # ---- flat arena -------------------------------------------------------------
-    def flatten_parameters(self, with_grad: bool = True) -> torch.Tensor:
-        """Make every parameter a view of one flat fp32 buffer (idempotent per device)."""
+    def flatten_parameters(self, with_grad: bool = False, channels_last: bool | None = None) -> torch.Tensor:
+        """Make every parameter a view of one flat fp32 buffer (idempotent per device).
+        On CUDA, 4-D (convolution) weights are stored channels-last inside their segment."""
         params = list(self.__model.parameters())
         assert params
         device = params[0].device
         if self.__flat is not None and self.__flat.device == device and self.is_flat():
             return self.__flat
+        if channels_last is None:
+            channels_last = device.type == "cuda" and os.environ.get("DLS_CHANNELS_LAST", "1") != "0"
         total = sum(p.numel() for p in params)
         flat = torch.empty(total, dtype=torch.float32, device=device)
         flat_grad = torch.zeros(total, dtype=torch.float32, device=device) if with_grad else None
@@ -160,8 +179,14 @@ class ModelUtil:
         with torch.no_grad():
             for p in params:
                 n = p.numel()
-                flat[off : off + n].copy_(p.data.reshape(-1))
-                p.data = flat[off : off + n].view(p.shape)
+                seg = flat[off : off + n]
+                if channels_last and p.dim() == 4 and p.shape[1] > 1 and (p.shape[2] > 1 or p.shape[3] > 1):
+                    o, c, h, w = p.shape
+                    view = seg.view(o, h, w, c).permute(0, 3, 1, 2)
+                else:
+                    view = seg.view(p.shape)
+                view.copy_(p.data)
+                p.data = view
                 if flat_grad is not None and p.requires_grad:
                     p.grad = flat_grad[off : off + n].view(p.shape)
                 off += n

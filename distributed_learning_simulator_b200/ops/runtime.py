@@ -33,8 +33,8 @@ _SIGNATURES = {
     "dls_sgd_step": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_float, c_float,
                      c_float, c_int, c_void_p],
     "dls_sgd_tick": [c_void_p, c_void_p],
-    "dls_gather_batch": [c_void_p, c_void_p, c_void_p, c_ll, c_void_p, c_int, c_int, c_int, c_ll, c_void_p,
-                         c_void_p, c_void_p],
+    "dls_gather_batch": [c_void_p, c_void_p, c_void_p, c_ll, c_void_p, c_int, c_int, c_int, c_ll, c_int,
+                         c_void_p, c_void_p, c_void_p],
     "dls_metric_accumulate": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p],
     "dls_sq_quant": [c_void_p, c_ll, c_void_p, c_int, c_int, c_u64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
     "dls_sq_dequant": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_ll, c_void_p, c_void_p],

@@ -21,10 +21,17 @@ def sgd_tick(state: torch.Tensor) -> None:
 
 def gather_batch(x_all: torch.Tensor, y_all: torch.Tensor, order: torch.Tensor, n_order: int, state: torch.Tensor,
                  state_index: int, x_out: torch.Tensor, y_out: torch.Tensor, batch_stride: int | None = None) -> None:
+    """``x_out`` may be a channels-last 4-D tensor: rows are then written H,W,C."""
     batch = x_out.shape[0]
     row = x_out[0].numel()
+    nhwc = 0
+    if x_out.dim() == 4 and not x_out.is_contiguous():
+        assert x_out.is_contiguous(memory_format=torch.channels_last)
+        nhwc = int(x_out.shape[1])
+    else:
+        assert x_out.is_contiguous()
     runtime.call("dls_gather_batch", x_all.data_ptr(), y_all.data_ptr(), order.data_ptr(), int(n_order),
-                 state.data_ptr(), int(state_index), int(batch), int(batch_stride or batch), int(row),
+                 state.data_ptr(), int(state_index), int(batch), int(batch_stride or batch), int(row), nhwc,
                  x_out.data_ptr(), y_out.data_ptr(),
                  runtime.stream_ptr(x_out.device))
 

@@ -7,7 +7,7 @@ from typing import Any
 import torch.distributed as dist
 
 from ..engine.log import add_file_handler, get_logger
-from ..engine.model_util import ModelUtil, ParameterLayout
+from ..engine.model_util import ModelUtil
 from .context import get_context, is_distributed  # noqa: F401
 
 
@@ -25,8 +25,9 @@ def train_distributed(config: Any, practitioners: None | set, task_id: int | Non
     config.parallel_number = 1
     if ctx.use_p2p:
         dc = config.create_dataset_collection()
-        model = config._create_model(dc)
-        layout = ParameterLayout.from_dict(ModelUtil(model).get_parameter_dict())
+        util = ModelUtil(config._create_model(dc).to(ctx.device))
+        util.flatten_parameters()  # same storage convention (channels-last conv weights) as every executor
+        layout = util.layout
         ctx.setup_arena(layout, config.worker_number)
     worker_config = get_worker_config(config, practitioners=practitioners)
     task = _Task(task_id, config, worker_config)

@@ -74,10 +74,11 @@ int dls_sgd_step(float* params, float* momentum_buf, const float* const* grads, 
 /* state[0] += 1 (schedule step); state[1] = 1 (momentum ready); state[2] += 1 (batch index in epoch) */
 int dls_sgd_tick(int32_t* state, void* stream);
 /* x_out[b,:] = x_all[order[state[state_index]*batch_stride + b], :] for b < batch, y likewise;
- * positions past n_order repeat the last entry */
+ * positions past n_order repeat the last entry.  nhwc_channels > 1: each C,H,W source row is
+ * written H,W,C (channels-last activations for the tensor-core convolutions) */
 int dls_gather_batch(const float* x_all, const long long* y_all, const long long* order, long long n_order,
                      const int32_t* state, int state_index, int batch, int batch_stride, long long row_elems,
-                     float* x_out, long long* y_out, void* stream);
+                     int nhwc_channels, float* x_out, long long* y_out, void* stream);
 /* acc[0] += loss*batch ; acc[1] += #(argmax(logits)==y) ; acc[2] += batch   (fp64 acc) */
 int dls_metric_accumulate(const float* logits, const long long* targets, const float* loss, int batch, int classes,
                           double* acc, void* stream);

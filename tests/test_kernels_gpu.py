@@ -216,6 +216,11 @@ def test_gather_and_metric(dev):
     ys = torch.empty(22, dtype=torch.int64, device=dev)
     S.gather_batch(x_all, y_all, order, 150, state, 2, xs, ys, batch_stride=32)
     assert torch.equal(xs, x_all[order[128:150]]) and torch.equal(ys, y_all[order[128:150]])
+    # channels-last destination: rows come out H,W,C
+    xc = torch.empty(32, 3, 8, 8, device=dev).contiguous(memory_format=torch.channels_last)
+    state[2] = 2
+    S.gather_batch(x_all, y_all, order, 150, state, 2, xc, y)
+    assert torch.equal(xc, x_all[idx]) and xc.is_contiguous(memory_format=torch.channels_last)
     logits = torch.randn(32, 10, device=dev)
     loss = torch.nn.functional.cross_entropy(logits, y).reshape(1)
     acc = torch.zeros(3, dtype=torch.float64, device=dev)

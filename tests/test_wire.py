@@ -62,3 +62,28 @@ def test_event_driven_wait_wakes_up():
     assert server.wait_for_data({0}, timeout=5.0) == {0}
     assert server.get(0).other_data["hello"]
     assert not client.has_data() and not client.wait_for_data(timeout=0.01)
+
+
+def test_layout_with_channels_last_segments():
+    import torch
+
+    conv = torch.nn.Conv2d(3, 4, 3)
+    fc = torch.nn.Linear(5, 2)
+    model = torch.nn.Sequential(conv, torch.nn.Flatten(), fc)
+    from distributed_learning_simulator_b200.engine.model_util import ModelUtil
+
+    util = ModelUtil(model)
+    ref = {k: v.clone() for k, v in util.get_parameter_dict().items()}
+    flat = util.flatten_parameters(channels_last=True)
+    layout = util.layout
+    assert layout.formats == [1, 0, 0, 0]
+    assert util.is_flat() and conv.weight.is_contiguous(memory_format=torch.channels_last)
+    for k, v in util.get_parameter_dict().items():
+        assert torch.equal(v, ref[k])
+    # the dict view of the flat vector is format aware, in both directions
+    fp = FlatParameter(flat.clone(), layout)
+    assert all(torch.equal(fp[k], ref[k]) for k in ref)
+    assert torch.equal(layout.flatten(ref), flat)
+    plain = ParameterLayout.from_dict(ref)
+    assert plain != layout and plain.formats == [0, 0, 0, 0]
+    assert ParameterLayout.from_dict(util.get_parameter_dict()) == layout
