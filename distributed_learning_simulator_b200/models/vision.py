@@ -10,6 +10,7 @@ from typing import Any
 import torch
 from torch import nn
 
+from ..ops.bn import bn_act
 from .registry import register_model
 
 
@@ -55,7 +56,7 @@ class _DenseLayer(nn.Module):
         self.conv = nn.Conv2d(in_ch, growth, kernel_size=3, padding=1, bias=False)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        return torch.cat([x, self.conv(self.relu(self.norm(x)))], dim=1)
+        return torch.cat([x, self.conv(bn_act(self.norm, x, relu=True))], dim=1)
 
 
 class _Transition(nn.Module):
@@ -67,7 +68,7 @@ class _Transition(nn.Module):
         self.pool = nn.AvgPool2d(2)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        return self.pool(self.conv(self.relu(self.norm(x))))
+        return self.pool(self.conv(bn_act(self.norm, x, relu=True)))
 
 
 class DenseNet40(nn.Module):
@@ -93,7 +94,7 @@ class DenseNet40(nn.Module):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         x = self.features(self.stem(x))
-        x = self.final_relu(self.final_norm(x))
+        x = bn_act(self.final_norm, x, relu=True)
         return self.classifier(self.flatten(self.pool(x)))
 
 
@@ -111,10 +112,9 @@ class _BasicBlock(nn.Module):
         self.relu2 = nn.ReLU(inplace=True)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        identity = x if self.downsample is None else self.downsample(x)
-        out = self.relu1(self.bn1(self.conv1(x)))
-        out = self.bn2(self.conv2(out))
-        return self.relu2(out + identity)
+        identity = x if self.downsample is None else bn_act(self.downsample[1], self.downsample[0](x))
+        out = bn_act(self.bn1, self.conv1(x), relu=True)
+        return bn_act(self.bn2, self.conv2(out), relu=True, residual=identity)
 
 
 class ResNet18(nn.Module):
@@ -136,7 +136,7 @@ class ResNet18(nn.Module):
         self.fc = nn.Linear(512, num_classes)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        x = self.relu(self.bn1(self.conv1(x)))
+        x = bn_act(self.bn1, self.conv1(x), relu=True)
         x = self.layers(x)
         return self.fc(self.flatten(self.pool(x)))
 

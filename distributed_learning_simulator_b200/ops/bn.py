@@ -1,0 +1,92 @@
+"""Fused training-mode BatchNorm (+ residual add) (+ ReLU) on channels-last activations
+(csrc/bn.cu): one cluster launch forward and one backward (statistics exchanged through
+distributed shared memory), instead of ATen's separate statistics / transform / ReLU / add kernels.  ``bn_act`` is what the vision models call; it falls back to
+the plain modules whenever the fused kernel does not apply (CPU, running statistics enabled,
+NCHW activations, odd channel counts)."""
+import os
+
+import torch
+from torch import nn
+
+from . import runtime
+
+_DTYPE = {torch.float32: 0, torch.bfloat16: 1}
+STATS = {"fused_fwd": 0, "fallback": 0}
+
+
+def _enabled() -> bool:
+    return os.environ.get("DLS_FUSED_BN", "1") != "0"
+
+
+def can_fuse(bn: nn.Module, x: torch.Tensor, residual: torch.Tensor | None) -> bool:
+    if not (_enabled() and x.is_cuda and x.dim() == 4 and x.dtype in _DTYPE and runtime.available()):
+        return False
+    if bn.track_running_stats or bn.running_mean is not None or not bn.affine:
+        return False  # the kernel implements the batch-statistics mode this framework trains in
+    c = x.shape[1]
+    vec = 8 if (x.dtype == torch.bfloat16 and c % 8 == 0) else 4
+    if c % 4 or c < 4:
+        return False
+    if not x.is_contiguous(memory_format=torch.channels_last):
+        return False
+    if residual is not None and (residual.dtype != x.dtype or residual.shape != x.shape
+                                 or not residual.is_contiguous(memory_format=torch.channels_last)):
+        return False
+    return True
+
+
+class _FusedBNAct(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, residual, eps, relu, bn):
+        n, c, h, w = x.shape
+        rows = n * h * w
+        dtype = _DTYPE[x.dtype]
+        y = torch.empty_like(x)  # preserves channels-last
+        mean = torch.empty(c, dtype=torch.float32, device=x.device)
+        invstd = torch.empty(c, dtype=torch.float32, device=x.device)
+        runtime.call("dls_bn_fwd", x.data_ptr(), dtype, rows, c, weight.data_ptr(), bias.data_ptr(),
+                     runtime.ptr(residual), float(eps), int(relu), y.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
+                     runtime.stream_ptr(x.device))
+        STATS["fused_fwd"] += 1
+        ctx.save_for_backward(x, y if relu else x, weight, mean, invstd)
+        ctx.relu, ctx.has_residual, ctx.bn = bool(relu), residual is not None, bn
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, y, weight, mean, invstd = ctx.saved_tensors
+        n, c, h, w = x.shape
+        rows = n * h * w
+        dtype = _DTYPE[x.dtype]
+        if dy.dtype != x.dtype or not dy.is_contiguous(memory_format=torch.channels_last):
+            dy = dy.to(x.dtype).contiguous(memory_format=torch.channels_last)
+        dx = torch.empty_like(x)
+        dres = torch.empty_like(x) if ctx.has_residual else None
+        dgamma = torch.empty(c, dtype=torch.float32, device=x.device)
+        dbeta = torch.empty(c, dtype=torch.float32, device=x.device)
+        runtime.call("dls_bn_bwd", dy.data_ptr(), y.data_ptr(), x.data_ptr(), dtype, rows, c, weight.data_ptr(),
+                     mean.data_ptr(), invstd.data_ptr(), int(ctx.relu), dx.data_ptr(), runtime.ptr(dres),
+                     dgamma.data_ptr(), dbeta.data_ptr(), runtime.stream_ptr(x.device))
+        return dx, dgamma, dbeta, dres, None, None, None
+
+
+def bn_act(bn: nn.Module, x: torch.Tensor, relu: bool = False, residual: torch.Tensor | None = None) -> torch.Tensor:
+    """``relu(bn(x) + residual)`` with batch statistics."""
+    if can_fuse(bn, x, residual):
+        return _FusedBNAct.apply(x, bn.weight, bn.bias, residual, bn.eps, relu, bn)
+    STATS["fallback"] += 1
+    out = bn(x)
+    if residual is not None:
+        out = out + residual
+    return torch.relu(out) if relu else out
+
+
+def oracle_bn_act(x, weight, bias, eps, relu, residual=None):
+    """Plain PyTorch fp32 statement of the same op (test oracle)."""
+    xf = x.float()
+    mean = xf.mean(dim=(0, 2, 3), keepdim=True)
+    var = xf.var(dim=(0, 2, 3), unbiased=False, keepdim=True)
+    out = (xf - mean) * torch.rsqrt(var + eps) * weight.view(1, -1, 1, 1) + bias.view(1, -1, 1, 1)
+    if residual is not None:
+        out = out + residual.float()
+    return torch.relu(out) if relu else out

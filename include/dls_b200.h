@@ -83,6 +83,19 @@ int dls_gather_batch(const float* x_all, const long long* y_all, const long long
 int dls_metric_accumulate(const float* logits, const long long* targets, const float* loss, int batch, int classes,
                           double* acc, void* stream);
 
+/* ---- fused training-mode BatchNorm (+residual) (+ReLU), channels-last activations ---------
+ *      (reference: BatchNorm/ReLU inside the external Trainer's model forward/backward;
+ *      batch statistics are always used, simulation_lib/util/model.py:23) ---------------------
+ * x/y/residual/dy/dx: [rows, channels] with channels contiguous (NHWC), dtype 0 = fp32,
+ * 1 = bf16; channels % 4 == 0.  One cluster launch each way: the CTAs that share a channel
+ * group combine their statistics through distributed shared memory.  fwd writes mean/invstd
+ * (fp32 [channels]) for bwd; bwd writes dgamma/dbeta (fp32 [channels]). */
+int dls_bn_fwd(const void* x, int dtype, long long rows, int channels, const float* gamma, const float* beta,
+               const void* residual, float eps, int relu, void* y, float* mean, float* invstd, void* stream);
+int dls_bn_bwd(const void* dy, const void* y, const void* x, int dtype, long long rows, int channels,
+               const float* gamma, const float* mean, const float* invstd, int relu, void* dx, void* dresidual,
+               float* dgamma, float* dbeta, void* stream);
+
 /* ---- quantizers (reference: topology/quantized_endpoint.py:76,82,89,102-104 and the
  *      external cyy_torch_algorithm.quantization; oracle in algorithm/quantization) ---- */
 int dls_sq_quant(const float* flat, long long n, const long long* tensor_offsets, int n_tensors, int level,

@@ -268,3 +268,44 @@ def test_block_sqdiff(dev):
     got = M.block_sqdiff(cur, prev, offsets, block_of, 5)
     ref = M.oracle_block_sqdiff(cur, prev, offsets, block_of, 5)
     torch.testing.assert_close(got, ref, rtol=1e-9, atol=1e-9)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("shape", [(64, 64, 32, 32), (7, 24, 5, 3), (3, 512, 4, 4), (16, 36, 8, 8)])
+@pytest.mark.parametrize("relu,with_res", [(True, False), (True, True), (False, False)])
+def test_fused_bn_act_matches_pytorch(dev, dtype, shape, relu, with_res):
+    from distributed_learning_simulator_b200.ops import bn as B
+
+    n, c, h, w = shape
+    g = torch.Generator(device="cuda").manual_seed(c + h)
+    bn = torch.nn.BatchNorm2d(c, track_running_stats=False).to(dev)
+    with torch.no_grad():
+        bn.weight.copy_(torch.rand(c, device=dev, generator=g) + 0.5)
+        bn.bias.copy_(torch.randn(c, device=dev, generator=g) * 0.1)
+    x = (torch.randn(shape, device=dev, generator=g) * 1.5 + 0.3).to(dtype).contiguous(memory_format=torch.channels_last)
+    res = torch.randn(shape, device=dev, generator=g).to(dtype).contiguous(memory_format=torch.channels_last) \
+        if with_res else None
+    dy = torch.randn(shape, device=dev, generator=g).to(dtype).contiguous(memory_format=torch.channels_last)
+    x1 = x.clone().requires_grad_(True)
+    r1 = res.clone().requires_grad_(True) if with_res else None
+    assert B.can_fuse(bn, x1, r1)
+    y = B.bn_act(bn, x1, relu=relu, residual=r1)
+    y.backward(dy)
+    got = (y, x1.grad, bn.weight.grad.clone(), bn.bias.grad.clone(), r1.grad if with_res else None)
+    bn.zero_grad()
+    x2 = x.float().clone().requires_grad_(True)
+    r2 = res.float().clone().requires_grad_(True) if with_res else None
+    pre = B.oracle_bn_act(x2, bn.weight, bn.bias, bn.eps, False, r2)
+    y_ref = torch.relu(pre) if relu else pre
+    # backward through the kernel's own ReLU mask: outputs within rounding of zero may differ
+    masked = pre * (y.detach().float() > 0).float() if relu else pre
+    masked.backward(dy.float())
+    tol = dict(rtol=2e-2, atol=2e-2) if dtype == torch.bfloat16 else dict(rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(got[0].float(), y_ref.detach(), **tol)
+    torch.testing.assert_close(got[1].float(), x2.grad, **(dict(rtol=5e-2, atol=5e-2) if dtype == torch.bfloat16 else tol))
+    scale = float(n * h * w) ** 0.5
+    gtol = dict(rtol=2e-2, atol=2e-2 * scale) if dtype == torch.bfloat16 else dict(rtol=1e-3, atol=1e-3 * scale)
+    torch.testing.assert_close(got[2], bn.weight.grad, **gtol)
+    torch.testing.assert_close(got[3], bn.bias.grad, **gtol)
+    if with_res:
+        torch.testing.assert_close(got[4].float(), r2.grad, **tol)
