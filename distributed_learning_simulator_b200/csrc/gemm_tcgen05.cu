@@ -1,0 +1,284 @@
+// bf16 GEMM on the 5th-generation tensor cores: C[b] = act(A[b] * B[b]^T + bias[b]).
+//
+// Used for the evaluation GEMMs (fully connected layers of the server's test pass) and for
+// the batched GTG-Shapley coalition evaluator, where the batch index b is the coalition
+// (reference path: one CPU model average + one full eager test inference per coalition,
+// simulation_lib/method/shapley_value/shapley_value_algorithm.py:67-76).
+//
+// Structure (sm_100a, one CTA per 128 x 64 output tile, no library GEMM):
+//   warp 0      TMA producer: cp.async.bulk.tensor loads of the A (128 x 64) and B (64 x 64)
+//               K-slices into a 4-stage 128B-swizzled shared-memory ring, mbarrier complete_tx
+//   warp 1      allocates TMEM, then one lane issues tcgen05.mma (M128 N64 K16, bf16 -> fp32
+//               accumulators in tensor memory); tcgen05.commit releases ring slots and finally
+//               signals the epilogue
+//   warps 2-5   epilogue: tcgen05.ld (32 lanes x 32 columns per instruction) -> bias / ReLU ->
+//               global stores (fp32 or bf16)
+// Out-of-range rows/columns/K are zero-filled by the TMA unit, so any M, N and any K % 8 == 0
+// work without padding copies.
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+#include "../../include/dls_b200.h"
+
+namespace dls {
+
+constexpr int kGemmBlockM = 128;
+constexpr int kGemmBlockN = 64;
+constexpr int kGemmBlockK = 64;   // 64 bf16 = 128 bytes = one swizzle atom row
+constexpr int kGemmUmmaK = 16;
+constexpr int kGemmStages = 4;
+constexpr int kGemmThreads = 192;
+constexpr uint32_t kBytesA = kGemmBlockM * kGemmBlockK * 2;
+constexpr uint32_t kBytesB = kGemmBlockN * kGemmBlockK * 2;
+constexpr uint32_t kTmemCols = 64;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// Bounded wait: a protocol bug must end in a trap (error reported to the host), not a hung GPU.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    const uint32_t addr = smem_u32(bar);
+    for (uint32_t spins = 0;; ++spins) {
+        uint32_t done;
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(addr), "r"(parity)
+            : "memory");
+        if (done) return;
+        if (spins > 20000000u) asm volatile("trap;");
+    }
+}
+
+__device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1,
+                                            int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+
+// K-major operand tile in shared memory, 128-byte swizzle: rows are 128 bytes apart, groups of
+// 8 rows 1024 bytes apart (SBO), LBO = 1 (unused for swizzled K-major), descriptor version 1.
+__device__ __forceinline__ uint64_t umma_smem_desc(uint32_t smem_addr) {
+    uint64_t desc = 0;
+    desc |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);   // start address, bits [0,14)
+    desc |= (uint64_t)1 << 16;                          // leading byte offset (>>4), bits [16,30)
+    desc |= (uint64_t)(1024 >> 4) << 32;                // stride byte offset (>>4), bits [32,46)
+    desc |= (uint64_t)1 << 46;                          // descriptor version (Blackwell)
+    desc |= (uint64_t)2 << 61;                          // layout type: SWIZZLE_128B
+    return desc;
+}
+
+// kind::f16 instruction descriptor: D = fp32, A = B = bf16, both K-major, M = 128, N = 64
+__device__ __forceinline__ uint32_t umma_instr_desc() {
+    uint32_t d = 0;
+    d |= 1u << 4;                         // c_format: F32
+    d |= 1u << 7;                         // a_format: BF16
+    d |= 1u << 10;                        // b_format: BF16
+    d |= (uint32_t)(kGemmBlockN >> 3) << 17;  // n_dim
+    d |= (uint32_t)(kGemmBlockM >> 4) << 24;  // m_dim
+    return d;
+}
+
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                          uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                 : "memory");
+}
+
+struct __align__(1024) GemmSmem {
+    __nv_bfloat16 a[kGemmStages][kGemmBlockM * kGemmBlockK];
+    __nv_bfloat16 b[kGemmStages][kGemmBlockN * kGemmBlockK];
+    uint64_t full[kGemmStages];
+    uint64_t empty[kGemmStages];
+    uint64_t tmem_full;
+    uint32_t tmem_base;
+};
+
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                         const float* __restrict__ bias, long long bias_batch_stride, void* __restrict__ c,
+                         int out_bf16, int m, int n, int k, int b_shared, int relu) {
+    extern __shared__ unsigned char smem_raw[];
+    GemmSmem& sm = *reinterpret_cast<GemmSmem*>(
+        (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = blockIdx.x * kGemmBlockM, n0 = blockIdx.y * kGemmBlockN, batch = blockIdx.z;
+    const int num_kb = (k + kGemmBlockK - 1) / kGemmBlockK;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+        for (int s = 0; s < kGemmStages; ++s) {
+            mbar_init(&sm.full[s], 1);
+            mbar_init(&sm.empty[s], 1);
+        }
+        mbar_init(&sm.tmem_full, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {  // whole warp: allocate the accumulator columns, then give the permit back
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm.tmem_base)),
+                     "r"(kTmemCols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_acc = sm.tmem_base;
+
+    if (warp == 0) {
+        if (lane == 0) {  // ---- TMA producer
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % kGemmStages;
+                const uint32_t phase = (kb / kGemmStages) & 1;
+                mbar_wait(&sm.empty[s], phase ^ 1);
+                mbar_expect_tx(&sm.full[s], kBytesA + kBytesB);
+                tma_load_3d(sm.a[s], &map_a, &sm.full[s], kb * kGemmBlockK, m0, batch);
+                tma_load_3d(sm.b[s], &map_b, &sm.full[s], kb * kGemmBlockK, n0, b_shared ? 0 : batch);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {  // ---- MMA issuer
+            const uint32_t idesc = umma_instr_desc();
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % kGemmStages;
+                const uint32_t phase = (kb / kGemmStages) & 1;
+                mbar_wait(&sm.full[s], phase);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t a_addr = smem_u32(sm.a[s]), b_addr = smem_u32(sm.b[s]);
+#pragma unroll
+                for (int kk = 0; kk < kGemmBlockK / kGemmUmmaK; ++kk) {
+                    // advancing 16 bf16 = 32 bytes along K stays inside the 128-byte swizzle row
+                    umma_bf16(tmem_acc, umma_smem_desc(a_addr + kk * kGemmUmmaK * 2),
+                              umma_smem_desc(b_addr + kk * kGemmUmmaK * 2), idesc, (kb | kk) != 0);
+                }
+                umma_commit(&sm.empty[s]);  // frees the ring slot when these MMAs have read it
+            }
+            umma_commit(&sm.tmem_full);     // accumulator complete
+        }
+    } else {
+        // ---- epilogue: warp w may touch TMEM lanes [32 * (w % 4), +32)
+        const int quarter = warp & 3;
+        const int row = m0 + quarter * 32 + lane;
+        mbar_wait(&sm.tmem_full, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const float* bias_b = bias != nullptr ? bias + (long long)batch * bias_batch_stride : nullptr;
+#pragma unroll
+        for (int chunk = 0; chunk < kGemmBlockN / 32; ++chunk) {
+            uint32_t r[32];
+            const uint32_t taddr = tmem_acc + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(chunk * 32);
+            asm volatile(
+                "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                  "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]),
+                  "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]),
+                  "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]),
+                  "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+                : "r"(taddr)
+                : "memory");
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            if (row < m) {
+                const int col0 = n0 + chunk * 32;
+                const long long out_off = ((long long)batch * m + row) * n + col0;
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const int col = col0 + j;
+                    if (col < n) {
+                        float v = __uint_as_float(r[j]);
+                        if (bias_b != nullptr) v += bias_b[col];
+                        if (relu) v = fmaxf(v, 0.f);
+                        if (out_bf16) reinterpret_cast<__nv_bfloat16*>(c)[out_off + j] = __float2bfloat16(v);
+                        else reinterpret_cast<float*>(c)[out_off + j] = v;
+                    }
+                }
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_acc), "r"(kTmemCols) : "memory");
+    }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return (EncodeTiledFn)p;
+    }();
+    return fn;
+}
+
+// [batch][rows][k] bf16, k contiguous; box = 64 (k) x box_rows x 1, 128-byte swizzle, zero fill
+static int make_map(CUtensorMap* map, const void* base, int rows, int k, int batch, int box_rows) {
+    EncodeTiledFn encode = get_encode_fn();
+    if (encode == nullptr) return fail_msg("cuTensorMapEncodeTiled is not available from this driver");
+    const cuuint64_t dims[3] = {(cuuint64_t)k, (cuuint64_t)rows, (cuuint64_t)batch};
+    const cuuint64_t strides[2] = {(cuuint64_t)k * 2, (cuuint64_t)rows * (cuuint64_t)k * 2};
+    const cuuint32_t box[3] = {(cuuint32_t)kGemmBlockK, (cuuint32_t)box_rows, 1};
+    const cuuint32_t elem_strides[3] = {1, 1, 1};
+    const CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box,
+                              elem_strides, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        snprintf(g_last_error, sizeof(g_last_error), "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+        return -1;
+    }
+    return 0;
+}
+
+}  // namespace dls
+
+using namespace dls;
+
+extern "C" int dls_gemm_bf16_tn(const void* a, const void* b, const float* bias, void* c, int out_dtype, int m, int n,
+                                int k, int batch, int b_shared, int relu, void* stream) {
+    if (m < 1 || n < 1 || k < 8 || batch < 1) return fail_msg("dls_gemm_bf16_tn: empty problem");
+    if (k % 8) return fail_msg("dls_gemm_bf16_tn: K must be a multiple of 8 (16-byte rows for TMA)");
+    if (((uintptr_t)a | (uintptr_t)b) & 15) return fail_msg("dls_gemm_bf16_tn: operands must be 16-byte aligned");
+    if (out_dtype != 0 && out_dtype != 1) return fail_msg("dls_gemm_bf16_tn: out_dtype must be 0 (fp32) or 1 (bf16)");
+    if (batch > 65535) return fail_msg("dls_gemm_bf16_tn: batch too large");
+    CUtensorMap map_a, map_b;
+    if (int rc = make_map(&map_a, a, m, k, batch, kGemmBlockM)) return rc;
+    if (int rc = make_map(&map_b, b, n, k, b_shared ? 1 : batch, kGemmBlockN)) return rc;
+    const size_t smem = sizeof(GemmSmem) + 1024;
+    static thread_local bool configured = false;
+    if (!configured) {
+        DLS_CHECK(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = true;
+    }
+    dim3 grid((m + kGemmBlockM - 1) / kGemmBlockM, (n + kGemmBlockN - 1) / kGemmBlockN, batch);
+    gemm_bf16_tcgen05_kernel<<<grid, kGemmThreads, smem, (cudaStream_t)stream>>>(
+        map_a, map_b, bias, b_shared ? 0 : (long long)n, c, out_dtype, m, n, k, b_shared, relu);
+    DLS_LAUNCHED("gemm_bf16_tcgen05_kernel");
+    return 0;
+}

@@ -1,0 +1,50 @@
+"""Front-end of the hand-written tcgen05 GEMM (csrc/gemm_tcgen05.cu).
+
+``linear_bf16(x, weight, bias)`` computes ``act(x @ weight.T + bias)`` with bf16 operands and
+fp32 accumulation in tensor memory; a leading batch dimension on ``x`` (and optionally on
+``weight``/``bias``) runs one independent GEMM per entry in the same launch -- the Shapley
+coalition evaluator uses that with batch = coalition."""
+import torch
+
+from . import runtime
+
+
+def available() -> bool:
+    return runtime.available()
+
+
+def linear_bf16(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor | None = None, relu: bool = False,
+                out_dtype: torch.dtype = torch.float32) -> torch.Tensor:
+    """x: [M, K] or [B, M, K]; weight: [N, K] or [B, N, K]; bias: [N] or [B, N]."""
+    assert x.is_cuda and x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16
+    squeeze = x.dim() == 2
+    if squeeze:
+        x = x.unsqueeze(0)
+    batch, m, k = x.shape
+    shared = weight.dim() == 2
+    n = weight.shape[-2]
+    assert weight.shape[-1] == k and (shared or weight.shape[0] == batch)
+    if k % 8:  # TMA rows must be 16-byte multiples: pad K with zeros (contributes nothing)
+        pad = 8 - k % 8
+        x = torch.nn.functional.pad(x, (0, pad))
+        weight = torch.nn.functional.pad(weight, (0, pad))
+        k += pad
+    x = x.contiguous()
+    weight = weight.contiguous()
+    if bias is not None:
+        bias = bias.float().contiguous()
+        assert bias.shape[-1] == n and (bias.dim() == 1) == shared
+    out = torch.empty((batch, m, n), dtype=out_dtype, device=x.device)
+    runtime.call("dls_gemm_bf16_tn", x.data_ptr(), weight.data_ptr(), runtime.ptr(bias), out.data_ptr(),
+                 0 if out_dtype == torch.float32 else 1, m, n, k, batch, int(shared), int(relu),
+                 runtime.stream_ptr(x.device))
+    return out[0] if squeeze else out
+
+
+def oracle_linear(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor | None = None,
+                  relu: bool = False) -> torch.Tensor:
+    """Plain PyTorch fp32 statement of the same op on the same (bf16-rounded) operands."""
+    out = torch.matmul(x.float(), weight.float().transpose(-1, -2))
+    if bias is not None:
+        out = out + (bias.float() if bias.dim() == 1 else bias.float().unsqueeze(-2))
+    return torch.relu(out) if relu else out

@@ -49,6 +49,8 @@ _SIGNATURES = {
     "dls_ipc_close_handle": [c_void_p],
     "dls_enable_peer_access": [c_int, c_int],
     "dls_copy_device": [c_void_p, c_void_p, c_ll, c_void_p],
+    "dls_gemm_bf16_tn": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                         c_void_p],
     "dls_bn_fwd": [c_void_p, c_int, c_ll, c_int, c_void_p, c_void_p, c_void_p, c_float, c_int, c_void_p, c_void_p,
                    c_void_p, c_void_p],
     "dls_bn_bwd": [c_void_p, c_void_p, c_void_p, c_int, c_ll, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p,

@@ -96,6 +96,16 @@ int dls_bn_bwd(const void* dy, const void* y, const void* x, int dtype, long lon
                const float* gamma, const float* mean, const float* invstd, int relu, void* dx, void* dresidual,
                float* dgamma, float* dbeta, void* stream);
 
+/* ---- bf16 GEMM on tcgen05 tensor cores, TMEM accumulators, TMA operand loads ------------
+ *      (reference: torch.nn.Linear inside the external Inferencer, server/server.py:40-55, and
+ *      one eager test inference per Shapley coalition, shapley_value_algorithm.py:67-76) -------
+ * c[b] = act(a[b] * B^T + bias): a [batch][m][k] bf16, b [batch | 1][n][k] bf16 (k contiguous:
+ * the torch Linear weight layout), bias [batch | 1][n] fp32 or NULL, c [batch][m][n] fp32
+ * (out_dtype 0) or bf16 (1).  k % 8 == 0, operands 16-byte aligned; m, n, k tails are
+ * zero-filled by TMA.  b_shared = 1: every batch entry uses the same b and bias. */
+int dls_gemm_bf16_tn(const void* a, const void* b, const float* bias, void* c, int out_dtype, int m, int n, int k,
+                     int batch, int b_shared, int relu, void* stream);
+
 /* ---- quantizers (reference: topology/quantized_endpoint.py:76,82,89,102-104 and the
  *      external cyy_torch_algorithm.quantization; oracle in algorithm/quantization) ---- */
 int dls_sq_quant(const float* flat, long long n, const long long* tensor_offsets, int n_tensors, int level,
