@@ -132,6 +132,8 @@ def reduce_rows_f32(rows: list[torch.Tensor], weights: list[float], old: torch.T
     rows = [r if r.device == device else r.to(device, non_blocking=True) for r in rows]
     if out is None:
         out = torch.empty(n, dtype=torch.float32, device=device)
+    assert out.is_contiguous() and out.data_ptr() % 16 == 0 and all(r.data_ptr() % 16 == 0 for r in rows), \
+        "fedavg_reduce_f32 uses 128-bit accesses: rows and output must be 16-byte aligned"
     row_table = runtime.pointer_table(rows, device)
     dst_table = (ctypes.c_void_p * 1)(out.data_ptr())  # host array: copied into the launch arguments
     w = torch.tensor(weights, dtype=torch.float32).pin_memory().to(device, non_blocking=True)

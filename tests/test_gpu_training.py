@@ -60,3 +60,31 @@ def test_smoke_entry():
     import __graft_entry__ as entry
 
     entry.smoke()
+
+
+def test_batched_coalition_evaluator_matches_sequential():
+    """GTG-Shapley on GPU: coalitions evaluated in batched launches (fused reduce + tcgen05 GEMMs)
+    give the same Shapley values as one-by-one evaluation, within the bf16 tolerance."""
+    from distributed_learning_simulator_b200 import load_config_from_dict, train
+    from distributed_learning_simulator_b200.ops import subset_eval
+    from distributed_learning_simulator_b200.training import get_last_training_result
+
+    results = {}
+    for batched in (True, False):
+        before = subset_eval.STATS["coalitions"]
+        config = load_config_from_dict(_conf(distributed_algorithm="GTG_shapley_value", worker_number=4, round=2,
+                                             epoch=1, learning_rate=0.1,
+                                             algorithm_kwargs={"batched_subset_eval": batched},
+                                             dataset_kwargs={"train_size": 1200, "test_size": 2000}))
+        train(config)
+        results[batched] = get_last_training_result()
+        used = subset_eval.STATS["coalitions"] - before
+        assert (used > 0) == batched
+    for rnd in (1, 2):
+        a, b = results[True]["sv"][rnd], results[False]["sv"][rnd]
+        assert set(a) == set(b) == {0, 1, 2, 3}
+        for w in a:
+            assert abs(a[w] - b[w]) < 0.02, (rnd, a, b)
+    for rnd in (0, 1, 2):
+        assert abs(results[True]["performance"][rnd]["test_accuracy"]
+                   - results[False]["performance"][rnd]["test_accuracy"]) < 1e-6
