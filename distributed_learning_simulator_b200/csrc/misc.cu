@@ -69,19 +69,36 @@ block_sqdiff_kernel(const float* __restrict__ cur, const float* __restrict__ pre
     __syncthreads();
     const long long n = s_off[n_tensors];
     const int lane = threadIdx.x & 31;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i - lane < n;
-         i += (long long)gridDim.x * blockDim.x) {
-        const bool valid = i < n;
-        const int b = valid ? block_of_tensor[find_segment(s_off, n_tensors, i)] : -1;
-        const float d = valid ? cur[i] - prev[i] : 0.f;
-        double sq = (double)d * d;
-        const int b0 = __shfl_sync(0xffffffffu, b, 0);
-        if (__all_sync(0xffffffffu, b == b0 || !valid) && b0 >= 0) {
+    constexpr int kIters = 64;  // a warp walks 2048 contiguous elements, one atomic at the end
+    const long long warp_id = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long n_warps = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long base = warp_id * (kIters * 32); base < n; base += n_warps * (kIters * 32)) {
+        int b_cur = -1;
+        long long t_end = -1;
+        double acc = 0.0;
+        for (int j = 0; j < kIters; ++j) {
+            const long long i = base + (long long)j * 32 + lane;
+            if (i >= n) break;
+            if (i >= t_end) {
+                const int t = find_segment(s_off, n_tensors, i);
+                t_end = s_off[t + 1];
+                const int b = block_of_tensor[t];
+                if (b != b_cur) {
+                    if (b_cur >= 0) atomicAdd(scores + b_cur, acc);
+                    b_cur = b;
+                    acc = 0.0;
+                }
+            }
+            const float d = cur[i] - prev[i];
+            if (b_cur >= 0) acc += (double)d * d;
+        }
+        const int b0 = __shfl_sync(0xffffffffu, b_cur, 0);
+        if (__all_sync(0xffffffffu, b_cur == b0) && b0 >= 0) {
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
-            if (lane == 0) atomicAdd(scores + b0, sq);
-        } else if (valid && b >= 0) {
-            atomicAdd(scores + b, sq);
+            for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+            if (lane == 0) atomicAdd(scores + b0, acc);
+        } else if (b_cur >= 0) {
+            atomicAdd(scores + b_cur, acc);
         }
     }
 }

@@ -20,6 +20,13 @@ __device__ __forceinline__ int float_to_ordered(float f) {
 __device__ __forceinline__ float ordered_to_float(int k) { return __int_as_float(k >= 0 ? k : k ^ 0x7fffffff); }
 
 // ---------------------------------------------------------------- stochastic (sq)
+// Segmented reductions over the flat arena share one access pattern: a warp walks a contiguous
+// span of kSpanIters * 32 elements, every lane keeps a private partial for the tensor it is
+// currently inside (flushing it with an atomic only when it crosses a tensor boundary), and at
+// the end of the span the lanes combine with shuffles and issue ONE atomic when they all sit in
+// the same tensor -- a few thousand atomics per model instead of one per 32 elements.
+constexpr int kSpanIters = 64;
+
 __global__ void __launch_bounds__(256)
 sq_absmax_kernel(const float* __restrict__ flat, long long n, const long long* __restrict__ tensor_offsets,
                  int n_tensors, uint32_t* __restrict__ absmax_bits) {
@@ -27,20 +34,30 @@ sq_absmax_kernel(const float* __restrict__ flat, long long n, const long long* _
     for (int i = threadIdx.x; i <= n_tensors; i += blockDim.x) s_off[i] = tensor_offsets[i];
     __syncthreads();
     const int lane = threadIdx.x & 31;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i - lane < n;
-         i += (long long)gridDim.x * blockDim.x) {
-        const bool valid = i < n;
-        const int t = valid ? find_segment(s_off, n_tensors, i) : -1;
-        float a = valid ? fabsf(flat[i]) : 0.f;
-        // warp-uniform tensor id is the common case: one atomic per warp
-        const int t0 = __shfl_sync(0xffffffffu, t, 0);
-        const bool uniform = __all_sync(0xffffffffu, t == t0 || !valid);
-        if (uniform && t0 >= 0) {
+    const long long warp_id = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long n_warps = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long base = warp_id * (kSpanIters * 32); base < n; base += n_warps * (kSpanIters * 32)) {
+        int t_cur = -1;
+        long long t_end = -1;
+        float acc = 0.f;
+        for (int j = 0; j < kSpanIters; ++j) {
+            const long long i = base + (long long)j * 32 + lane;
+            if (i >= n) break;
+            if (i >= t_end) {
+                if (t_cur >= 0) atomicMax(absmax_bits + t_cur, __float_as_uint(acc));
+                t_cur = find_segment(s_off, n_tensors, i);
+                t_end = s_off[t_cur + 1];
+                acc = 0.f;
+            }
+            acc = fmaxf(acc, fabsf(flat[i]));
+        }
+        const int t0 = __shfl_sync(0xffffffffu, t_cur, 0);
+        if (__all_sync(0xffffffffu, t_cur == t0) && t0 >= 0) {
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) a = fmaxf(a, __shfl_xor_sync(0xffffffffu, a, o));
-            if (lane == 0) atomicMax(absmax_bits + t0, __float_as_uint(a));
-        } else if (valid) {
-            atomicMax(absmax_bits + t, __float_as_uint(a));
+            for (int o = 16; o > 0; o >>= 1) acc = fmaxf(acc, __shfl_xor_sync(0xffffffffu, acc, o));
+            if (lane == 0) atomicMax(absmax_bits + t0, __float_as_uint(acc));
+        } else if (t_cur >= 0) {
+            atomicMax(absmax_bits + t_cur, __float_as_uint(acc));
         }
     }
 }
@@ -133,6 +150,13 @@ __global__ void nnadq_init_kernel(NnadqStats* stats, int n_tensors) {
     }
 }
 
+__device__ __forceinline__ void nnadq_flush(NnadqStats* stats, int t, float mn, float mx, double s, double ss) {
+    atomicMin(&stats[t].min_key, float_to_ordered(mn));
+    atomicMax(&stats[t].max_key, float_to_ordered(mx));
+    atomicAdd(&stats[t].sum, s);
+    atomicAdd(&stats[t].sumsq, ss);
+}
+
 __global__ void __launch_bounds__(256)
 nnadq_stats_kernel(const float* __restrict__ flat, const long long* __restrict__ tensor_offsets, int n_tensors,
                    NnadqStats* __restrict__ stats) {
@@ -141,34 +165,40 @@ nnadq_stats_kernel(const float* __restrict__ flat, const long long* __restrict__
     __syncthreads();
     const long long n = s_off[n_tensors];
     const int lane = threadIdx.x & 31;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i - lane < n;
-         i += (long long)gridDim.x * blockDim.x) {
-        const bool valid = i < n;
-        const int t = valid ? find_segment(s_off, n_tensors, i) : -1;
-        const float x = valid ? flat[i] : 0.f;
-        const int t0 = __shfl_sync(0xffffffffu, t, 0);
-        const bool uniform = __all_sync(0xffffffffu, t == t0);
-        if (uniform && t0 >= 0) {
-            float mn = x, mx = x;
-            double s = x, ss = (double)x * x;
+    const long long warp_id = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long n_warps = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long base = warp_id * (kSpanIters * 32); base < n; base += n_warps * (kSpanIters * 32)) {
+        int t_cur = -1;
+        long long t_end = -1;
+        float mn = INFINITY, mx = -INFINITY;
+        double sum = 0.0, sq = 0.0;
+        for (int j = 0; j < kSpanIters; ++j) {
+            const long long i = base + (long long)j * 32 + lane;
+            if (i >= n) break;
+            if (i >= t_end) {
+                if (t_cur >= 0) nnadq_flush(stats, t_cur, mn, mx, sum, sq);
+                t_cur = find_segment(s_off, n_tensors, i);
+                t_end = s_off[t_cur + 1];
+                mn = INFINITY; mx = -INFINITY; sum = 0.0; sq = 0.0;
+            }
+            const float x = flat[i];
+            mn = fminf(mn, x);
+            mx = fmaxf(mx, x);
+            sum += x;
+            sq += (double)x * x;
+        }
+        const int t0 = __shfl_sync(0xffffffffu, t_cur, 0);
+        if (__all_sync(0xffffffffu, t_cur == t0) && t0 >= 0) {
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) {
                 mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
                 mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-                s += __shfl_xor_sync(0xffffffffu, s, o);
-                ss += __shfl_xor_sync(0xffffffffu, ss, o);
+                sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                sq += __shfl_xor_sync(0xffffffffu, sq, o);
             }
-            if (lane == 0) {
-                atomicMin(&stats[t0].min_key, float_to_ordered(mn));
-                atomicMax(&stats[t0].max_key, float_to_ordered(mx));
-                atomicAdd(&stats[t0].sum, s);
-                atomicAdd(&stats[t0].sumsq, ss);
-            }
-        } else if (valid) {
-            atomicMin(&stats[t].min_key, float_to_ordered(x));
-            atomicMax(&stats[t].max_key, float_to_ordered(x));
-            atomicAdd(&stats[t].sum, (double)x);
-            atomicAdd(&stats[t].sumsq, (double)x * x);
+            if (lane == 0) nnadq_flush(stats, t0, mn, mx, sum, sq);
+        } else if (t_cur >= 0) {
+            nnadq_flush(stats, t_cur, mn, mx, sum, sq);
         }
     }
 }
