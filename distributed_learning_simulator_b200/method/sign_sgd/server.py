@@ -16,7 +16,8 @@ class SignSGDServer(Server):
         kwargs.pop("algorithm", None)
         super().__init__(**kwargs)
         self.algorithm = None
-        self.__pending: dict[int, Message] = {}
+        self.__gradients: dict[int, Message] = {}
+        self.__epoch_reports: dict[int, Message] = {}
         self.__finished: set[int] = set()
         self.__stat: dict = {}
         self.vote_count = 0
@@ -29,29 +30,34 @@ class SignSGDServer(Server):
         return len(self.__finished) == self.worker_number
 
     def _process_worker_data(self, worker_id: int, data: Message) -> None:
+        """Workers step in lock-step, but shards need not hold the same number of batches: a worker
+        that has finished its epoch waits for the epoch acknowledgement while the others keep
+        voting among themselves."""
         if data.end_training:
             self.__finished.add(worker_id)
-            return
-        self.__pending[worker_id] = data
-        if len(self.__pending) < self.worker_number - len(self.__finished):
-            return
-        pending, self.__pending = self.__pending, {}
-        first = next(iter(pending.values()))
-        if "gradient" in first.other_data:
-            n = int(first.other_data["numel"])
-            rows = [pending[w].other_data["gradient"] for w in sorted(pending)]
+        elif "gradient" in data.other_data:
+            self.__gradients[worker_id] = data
+        else:
+            self.__epoch_reports[worker_id] = data
+        active = set(range(self.worker_number)) - self.__finished
+        stepping = active - set(self.__epoch_reports)
+        if stepping and all(w in self.__gradients for w in stepping):
+            gradients, self.__gradients = self.__gradients, {}
+            n = int(next(iter(gradients.values())).other_data["numel"])
+            rows = [gradients[w].other_data["gradient"] for w in sorted(gradients)]
             vote = misc_ops.sign_majority(rows, n)
             self.vote_count += 1
-            self._endpoint.broadcast(Message(in_round=True, other_data={"gradient": vote}), worker_ids=set(pending))
-            return
-        epoch = first.other_data["epoch"]
-        for msg in pending.values():
-            if isinstance(msg, ParameterMessage):
-                self.tester.set_visualizer_prefix(f"epoch: {epoch},")
-                metric = self.get_metric(msg.parameter)
-                self.__stat[epoch] = {f"test_{k}": v for k, v in metric.items()}
-                get_logger().info("epoch: %s, test loss: %e, test accuracy: %.2f%%", epoch, metric["loss"],
-                                  metric["accuracy"] * 100)
-                with open(os.path.join(self.save_dir, "round_record.json"), "wt", encoding="utf8") as f:
-                    json.dump(self.__stat, f)
-        self._endpoint.broadcast(Message(in_round=True, other_data={"epoch": epoch}), worker_ids=set(pending))
+            self._endpoint.broadcast(Message(in_round=True, other_data={"gradient": vote}), worker_ids=set(gradients))
+        if active and all(w in self.__epoch_reports for w in active):
+            reports, self.__epoch_reports = self.__epoch_reports, {}
+            epoch = next(iter(reports.values())).other_data["epoch"]
+            for msg in reports.values():
+                if isinstance(msg, ParameterMessage):
+                    self.tester.set_visualizer_prefix(f"epoch: {epoch},")
+                    metric = self.get_metric(msg.parameter)
+                    self.__stat[epoch] = {f"test_{k}": v for k, v in metric.items()}
+                    get_logger().info("epoch: %s, test loss: %e, test accuracy: %.2f%%", epoch, metric["loss"],
+                                      metric["accuracy"] * 100)
+                    with open(os.path.join(self.save_dir, "round_record.json"), "wt", encoding="utf8") as f:
+                        json.dump(self.__stat, f)
+            self._endpoint.broadcast(Message(in_round=True, other_data={"epoch": epoch}), worker_ids=set(reports))

@@ -23,10 +23,11 @@ def gather_batch(x_all: torch.Tensor, y_all: torch.Tensor, order: torch.Tensor, 
                  state_index: int, x_out: torch.Tensor, y_out: torch.Tensor, batch_stride: int | None = None) -> None:
     """``x_out`` may be a channels-last 4-D tensor: rows are then written H,W,C."""
     batch = x_out.shape[0]
-    row = x_out[0].numel()
+    assert x_out.dtype == x_all.dtype and x_out.element_size() % 4 == 0
+    row = x_out[0].numel() * (x_out.element_size() // 4)  # rows are copied as 32-bit words (token ids: 2 per id)
     nhwc = 0
     if x_out.dim() == 4 and not x_out.is_contiguous():
-        assert x_out.is_contiguous(memory_format=torch.channels_last)
+        assert x_out.is_contiguous(memory_format=torch.channels_last) and x_out.element_size() == 4
         nhwc = int(x_out.shape[1])
     else:
         assert x_out.is_contiguous()
