@@ -117,21 +117,18 @@ def run_ours(args) -> dict:
         sampler = ClockSampler(gpu_index=local_rank) if (mode == "device" and rank == 0) else None
         timer = RoundTimer(args.warmup, args.steps, sampler)
         add_round_observer(timer)
-        graph_step.REPLAY_COUNTER[0] = 0
         PerformanceMetric.d2h_bytes = 0
-        replay0 = [0]
-
-        def mark(server, r, replay0=replay0, timer=timer):
-            if r == timer.warmup:
-                replay0[0] = graph_step.REPLAY_COUNTER[0]
-
-        add_round_observer(mark)
+        counters0 = (runtime.launch_count(), graph_step.CAPTURE_LAUNCHES[0], graph_step.OWN_REPLAYED_KERNELS[0])
         config = bench_config(n_workers, rounds, storage)
         try:
             train(config)
         finally:
             remove_round_observer(timer)
-            remove_round_observer(mark)
+        # every round launches the same kernels, so the timed rounds' share of the run's exact totals
+        # (taken after all role threads have finished) is exact; warm-up/capture launches are excluded
+        direct = (runtime.launch_count() - counters0[0]) - (graph_step.CAPTURE_LAUNCHES[0] - counters0[1])
+        replayed = graph_step.OWN_REPLAYED_KERNELS[0] - counters0[2]
+        launches = (direct + replayed) * args.steps / rounds
         clocks = sampler.stop() if sampler is not None else None
         assert timer.done.is_set(), "the timed rounds did not complete"
         ms = timer.elapsed_ms()
@@ -142,15 +139,14 @@ def run_ours(args) -> dict:
         h2d = graph_step.H2D_BYTES[0]
         d2h = PerformanceMetric.d2h_bytes
         if world > 1:
-            t = torch.tensor([h2d, d2h], dtype=torch.float64, device="cuda")
-            torch.distributed.all_reduce(t)
-            h2d, d2h = float(t[0].item()), float(t[1].item())
+            t = torch.tensor([h2d, d2h, launches], dtype=torch.float64, device="cuda")
+            torch.distributed.all_reduce(t)  # whole-job totals
+            h2d, d2h, launches = float(t[0].item()), float(t[1].item()), float(t[2].item())
         samples = TRAIN_PER_WORKER * n_workers * args.steps
-        replays = graph_step.REPLAY_COUNTER[0] - replay0[0]
         results[mode] = {
             "ms": ms, "samples_per_s": samples / (ms / 1e3), "rounds_per_s": args.steps / (ms / 1e3),
             "wall_ms": (timer.wall[1] - timer.wall[0]) * 1e3, "clocks": clocks,
-            "launches": (timer.launches[1] - timer.launches[0]) + replays * graph_step.KERNELS_PER_REPLAY,
+            "launches": launches,
             "h2d_bytes_per_step": h2d / max(rounds, 1) if storage == "pinned_host" else 0,
             "d2h_bytes_per_step": d2h / max(rounds, 1),
         }

@@ -33,7 +33,8 @@ _capture_lock = threading.Lock()
 # process-wide counters read by bench.py
 REPLAY_COUNTER = [0]
 H2D_BYTES = [0]
-KERNELS_PER_REPLAY = 4  # gather_batch, sgd_step, sgd_tick, metric_accumulate
+OWN_REPLAYED_KERNELS = [0]  # hand-written kernels executed through graph replays
+CAPTURE_LAUNCHES = [0]      # launch-counter increments that happened while warming up / capturing
 
 
 def _same_physical_layout(a: torch.Tensor, b: torch.Tensor) -> bool:
@@ -48,6 +49,7 @@ class _CapturedStep:
         self.y: torch.Tensor | None = None
         self.grad_table: torch.Tensor | None = None
         self.grads: list = []
+        self.own_kernels = 0
 
 
 class GraphTrainStep:
@@ -117,7 +119,10 @@ class GraphTrainStep:
 
     def _capture(self, batch: int, x_all: torch.Tensor, y_all: torch.Tensor, n_order: int) -> _CapturedStep:
         with _capture_lock:
-            return self._capture_locked(batch, x_all, y_all, n_order)
+            before = runtime.launch_count()
+            step = self._capture_locked(batch, x_all, y_all, n_order)
+            CAPTURE_LAUNCHES[0] += runtime.launch_count() - before
+            return step
 
     def _capture_locked(self, batch: int, x_all: torch.Tensor, y_all: torch.Tensor, n_order: int) -> _CapturedStep:
         t = self.trainer
@@ -143,8 +148,10 @@ class GraphTrainStep:
             p.grad = None
         torch.cuda.synchronize(self.device)
         graph = torch.cuda.CUDAGraph()
+        own_before = runtime.launch_count()
         with torch.cuda.graph(graph, capture_error_mode="thread_local"):
             self._one_step(step, x_all, y_all, n_order)
+        step.own_kernels = runtime.launch_count() - own_before  # own kernel nodes in one replay
         self._fill_grad_table(step)
         self.flat.copy_(saved[0])
         self.momentum_buf.copy_(saved[1])
@@ -205,6 +212,8 @@ class GraphTrainStep:
                     self.steps[key_rem].graph.replay()
                 self.replays += steps_per_epoch
                 REPLAY_COUNTER[0] += steps_per_epoch
+                OWN_REPLAYED_KERNELS[0] += full * self.steps[key_full].own_kernels if full else 0
+                OWN_REPLAYED_KERNELS[0] += self.steps[key_rem].own_kernels if rem else 0
                 self._host_step += steps_per_epoch
                 t.performance_metric.start_epoch(self.device)
                 t.performance_metric.accumulator.copy_(self.acc)
