@@ -74,7 +74,44 @@ fedavg_reduce_f32_kernel(const float* const* __restrict__ rows, const float* __r
     const long long n_vec = n >> 2;
     const long long stride = (long long)gridDim.x * blockDim.x;
     // [lo, hi) is 4-aligned on both ends except for the global tail, handled below
-    for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < n_vec; v += stride) {
+    long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (n_rows <= 4) {
+        // few rows (e.g. one worker per GPU on 2-4 GPUs): keep 4 positions x n_rows 128-bit loads
+        // in flight per thread -- peer loads over NVLink have ~2 us latency
+        for (; v + 3 * stride < n_vec; v += 4 * stride) {
+            double acc[4][4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { acc[u][0] = acc[u][1] = acc[u][2] = acc[u][3] = 0.0; }
+            for (int k = 0; k < n_rows; ++k) {
+                const float* row = s_rows[k] + lo;
+                float4 x[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    x[u] = kPeer ? ld_peer_f4(row + ((v + u * stride) << 2)) : ld_stream_f4(row + ((v + u * stride) << 2));
+                const double w = s_w[k];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    acc[u][0] += w * x[u].x; acc[u][1] += w * x[u].y; acc[u][2] += w * x[u].z; acc[u][3] += w * x[u].w;
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const long long i = lo + ((v + u * stride) << 2);
+                float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (old != nullptr) o = ld_stream_f4(old + i);
+                float4 r;
+                r.x = (float)((double)old_scale * o.x + acc[u][0] * inv_total);
+                r.y = (float)((double)old_scale * o.y + acc[u][1] * inv_total);
+                r.z = (float)((double)old_scale * o.z + acc[u][2] * inv_total);
+                r.w = (float)((double)old_scale * o.w + acc[u][3] * inv_total);
+                saw_nan |= (r.x != r.x) | (r.y != r.y) | (r.z != r.z) | (r.w != r.w);
+#pragma unroll
+                for (int d = 0; d < kMaxDsts; ++d)
+                    if (d < n_dsts) st_stream_f4(dsts.p[d] + i, r);
+            }
+        }
+    }
+    for (; v < n_vec; v += stride) {
         const long long i = lo + (v << 2);
         double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
         int k = 0;

@@ -48,3 +48,33 @@ def oracle_linear(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor | No
     if bias is not None:
         out = out + (bias.float() if bias.dim() == 1 else bias.float().unsqueeze(-2))
     return torch.relu(out) if relu else out
+
+
+STATS = {"linear_calls": 0}
+
+
+def install_inference_linear(model: torch.nn.Module) -> int:
+    """Route every ``nn.Linear`` of an evaluation-only model through the tcgen05 GEMM.
+
+    Applies when the call runs without autograd on CUDA (the server's test pass); training calls
+    and CPU calls keep the stock path.  bf16 operands, fp32 accumulation and fp32 logits -- the
+    same precision class as the bf16 autocast the evaluation otherwise runs under.
+    Returns the number of layers patched."""
+    import types
+
+    def forward(self: torch.nn.Linear, x: torch.Tensor) -> torch.Tensor:
+        if x.is_cuda and not torch.is_grad_enabled() and available() and x.dim() >= 2 \
+                and x.dtype in (torch.bfloat16, torch.float32) and torch.is_autocast_enabled():
+            lead = x.shape[:-1]
+            out = linear_bf16(x.reshape(-1, x.shape[-1]).to(torch.bfloat16), self.weight.to(torch.bfloat16), self.bias)
+            STATS["linear_calls"] += 1
+            return out.view(*lead, out.shape[-1])
+        return torch.nn.functional.linear(x, self.weight, self.bias)
+
+    patched = 0
+    for module in model.modules():
+        if type(module) is torch.nn.Linear and not getattr(module, "_dls_tcgen05", False):
+            module.forward = types.MethodType(forward, module)
+            module._dls_tcgen05 = True
+            patched += 1
+    return patched

@@ -131,6 +131,7 @@ class DistributedContext:
         self.peer_reads_pending = False
         self._flag_table: torch.Tensor | None = None
         self.p2p_reductions = 0
+        self._table_cache: dict = {}
         get_logger().debug("rank %s/%s on %s, p2p=%s", self.rank, self.world, self.device, self.use_p2p)
 
     # ---- ownership --------------------------------------------------------------------
@@ -186,8 +187,16 @@ class DistributedContext:
             raise RuntimeError("old model aliases the destination buffer")
         chunk = ((-(-n // self.world)) + 3) // 4 * 4
         lo, hi = min(self.rank * chunk, n), min((self.rank + 1) * chunk, n)
-        rows = runtime.pointer_table([p.ptr for p in payloads], self.device)
-        w = torch.tensor(weights, dtype=torch.float32).pin_memory().to(self.device, non_blocking=True)
+        # the same arena slots and dataset sizes come back every round: keep the tiny device tables
+        key = (tuple(p.ptr for p in payloads), tuple(weights))
+        cached = self._table_cache.get(key)
+        if cached is None:
+            if len(self._table_cache) > 64:
+                self._table_cache.clear()
+            cached = (runtime.pointer_table([p.ptr for p in payloads], self.device),
+                      torch.tensor(weights, dtype=torch.float32).pin_memory().to(self.device, non_blocking=True))
+            self._table_cache[key] = cached
+        rows, w = cached
         dsts = (ctypes.c_void_p * self.world)(*[self.globals.ptr(r, off) for r in range(self.world)])
         self.epoch += 1
         self._nan.zero_()

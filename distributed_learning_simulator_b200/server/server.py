@@ -52,6 +52,10 @@ class Server(Executor):
         tester.dataset_collection.remove_dataset(phase=MachineLearningPhase.Training)
         tester.dataset_collection.remove_dataset(phase=MachineLearningPhase.Validation)
         tester.hook_config.summarize_executor = False
+        if tester.hook_config.use_fused_kernels:
+            from ..ops import gemm
+
+            gemm.install_inference_linear(tester.model)  # evaluation GEMMs on the hand-written tcgen05 kernel
         if self._dist is not None:
             # every replica evaluates its shard of the test split; the sums are all-reduced
             tester.shard(self._dist.rank, self._dist.world, self._dist)

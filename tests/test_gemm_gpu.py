@@ -39,3 +39,23 @@ def test_linear_bf16_batched_and_bf16_out():
     # back-to-back launches reuse TMEM columns and barriers correctly
     again = G.linear_bf16(x, w[0], b[0])
     assert torch.equal(shared, again)
+
+
+def test_inference_linear_patch_matches_torch():
+    from distributed_learning_simulator_b200.ops import gemm as G
+
+    dev = torch.device("cuda", 0)
+    model = torch.nn.Sequential(torch.nn.Linear(512, 100), torch.nn.ReLU(), torch.nn.Linear(100, 10)).to(dev)
+    x = torch.randn(1250, 512, device=dev)
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        ref = model(x).float()
+    assert G.install_inference_linear(model) == 2
+    before = G.STATS["linear_calls"]
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        out = model(x).float()
+    assert G.STATS["linear_calls"] - before == 2
+    torch.testing.assert_close(out, ref, rtol=2e-2, atol=2e-2)
+    assert (out.argmax(1) == ref.argmax(1)).float().mean() > 0.99
+    y = model(x)  # autograd path is untouched
+    y.sum().backward()
+    assert model[0].weight.grad is not None and G.STATS["linear_calls"] - before == 2
