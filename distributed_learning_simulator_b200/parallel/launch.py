@@ -13,7 +13,7 @@ from .context import get_context, is_distributed  # noqa: F401
 
 def train_distributed(config: Any, practitioners: None | set, task_id: int | None) -> None:
     from ..algorithm_factory import get_worker_config
-    from ..training import _Task, _last_results
+    from ..training import _Task, _last_results, _write_trace
 
     ctx = get_context()
     shared = [config.save_dir, config.log_file]
@@ -35,6 +35,8 @@ def train_distributed(config: Any, practitioners: None | set, task_id: int | Non
     task.start()
     task.wait()
     task.raise_errors()
+    if ctx.rank == 0:
+        _write_trace(config)
     _last_results.clear()
     _last_results.update(task.results)
     _last_results["save_dir"] = config.save_dir

@@ -19,6 +19,7 @@ from ..engine.log import get_logger
 from ..engine.tensor import TensorDict, tensor_to
 from ..message import Message, ParameterMessage, ParameterMessageBase
 from ..util.model_cache import ModelCache
+from ..utils import tracing
 from .server import Server
 
 
@@ -89,7 +90,8 @@ class AggregationServer(Server):
                                self.worker_number)
 
     def _aggregate_worker_data(self) -> Any:
-        return self.__algorithm.aggregate_worker_data()
+        with tracing.phase("aggregate"):
+            return self.__algorithm.aggregate_worker_data()
 
     def _before_send_result(self, result: Message) -> None:
         if not isinstance(result, ParameterMessageBase):
@@ -139,7 +141,8 @@ class AggregationServer(Server):
 
     def _record_compute_stat(self, parameter_dict: TensorDict, keep_performance_logger: bool = True) -> None:
         self.tester.set_visualizer_prefix(f"round: {self._round_number},")
-        metric = self.get_metric(parameter_dict, keep_performance_logger=keep_performance_logger)
+        with tracing.phase("evaluate"):
+            metric = self.get_metric(parameter_dict, keep_performance_logger=keep_performance_logger)
         round_stat = {f"test_{k}": v for k, v in metric.items()}
         key = self._get_stat_key()
         assert key not in self.__stat

@@ -151,7 +151,10 @@ class Server(Executor):
         selected_workers = self._select_workers()
         get_logger().debug("choose workers %s", selected_workers)
         if selected_workers:
-            self._endpoint.broadcast(data=result, worker_ids=selected_workers)
+            from ..utils import tracing
+
+            with tracing.phase("broadcast"):
+                self._endpoint.broadcast(data=result, worker_ids=selected_workers)
         unselected_workers = set(range(self.worker_number)) - selected_workers
         if unselected_workers:
             self._endpoint.broadcast(data=None, worker_ids=unselected_workers)

@@ -127,6 +127,7 @@ def train(config: Any, practitioners: None | set = None) -> int | None:
         return task_id
     task.wait()
     task.raise_errors()
+    _write_trace(config)
     _last_results.clear()
     _last_results.update(task.results)
     _last_results["save_dir"] = config.save_dir
@@ -135,6 +136,20 @@ def train(config: Any, practitioners: None | set = None) -> int | None:
 
 
 _last_results: dict = {}
+
+
+def _write_trace(config: Any) -> None:
+    """Per-phase device timings of the run (DLS_TRACE=1), written once every role has finished."""
+    from .utils import tracing
+
+    if not tracing.enabled():
+        return
+    import json
+
+    path = os.path.join(config.save_dir, "server")
+    os.makedirs(path, exist_ok=True)
+    with open(os.path.join(path, "trace.json"), "wt", encoding="utf8") as f:
+        json.dump(tracing.summary(), f, indent=1)
 
 
 def get_last_training_result() -> dict:

@@ -59,7 +59,10 @@ class AggregationWorker(Client):
         self.trainer.append_named_hook(self._aggregation_time, "aggregation", __aggregation_impl)
 
     def _aggregation(self, sent_data: Message, **kwargs: Any) -> None:
-        self.send_data_to_server(sent_data)
+        from ..utils import tracing
+
+        with tracing.phase("upload"):
+            self.send_data_to_server(sent_data)
         self._offload_from_device()
         self._get_result_from_server()
 

@@ -17,6 +17,7 @@ import dill
 from ..engine.log import get_logger
 from ..engine.trainer import Trainer
 from ..executor import Executor
+from ..utils import tracing
 from ..practitioner import Practitioner
 from ..topology.endpoint import ClientEndpoint
 
@@ -77,7 +78,8 @@ class Worker(Executor):
                         self.trainer.hook_config.summarize_executor = False
                     self.trainer.disable_hook("batch_loss_logger")
                     self.trainer.set_visualizer_prefix(prefix=f"round: {self._round_num},")
-                    self.trainer.train(**kwargs)
+                    with tracing.phase("local_train"):
+                        self.trainer.train(**kwargs)
                     self._round_num += 1
                 self.trainer.wait_stream()
             get_logger().debug("finish worker")
