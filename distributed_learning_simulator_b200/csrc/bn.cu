@@ -316,6 +316,251 @@ bn_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* __rest
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Row-major ("wide") variant for activations with many rows and few channels (ResNet 64/128
+// channel stages): a CTA owns ALL channels of a slice of rows, so a warp reads whole rows
+// (512 contiguous bytes per instruction) instead of a 16-byte column strip of 32 different rows.
+// Partial statistics are folded inside the CTA, then across the cluster through DSMEM; one partial
+// per cluster goes to a small global scratch and the elementwise kernel folds those (<= 32) while
+// it builds its per-channel scale/shift table in shared memory.  Two launches each way.
+constexpr int kWideThreads = 512;
+constexpr int kWideCluster = 8;
+constexpr int kWideMaxClusters = 32;
+
+// block-level fold of per-thread partials over the threads that own the same channel vector
+template <int V>
+__device__ __forceinline__ void wide_block_fold(int cv, const float (&a)[V], const float (&b)[V], float* s_buf,
+                                                float* s_part, int channels) {
+    // s_buf: [kWideThreads][2V]
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+        s_buf[threadIdx.x * 2 * V + i] = a[i];
+        s_buf[threadIdx.x * 2 * V + V + i] = b[i];
+    }
+    __syncthreads();
+    const int rows_in_block = kWideThreads / cv;
+    for (int j = threadIdx.x; j < cv * 2 * V; j += kWideThreads) {
+        const int vec = j / (2 * V), k = j % (2 * V);
+        float acc = 0.f;
+        for (int r = 0; r < rows_in_block; ++r) acc += s_buf[(r * cv + vec) * 2 * V + k];
+        const int q = k / V, i = k % V;
+        s_part[q * channels + vec * V + i] = acc;
+    }
+}
+
+template <typename T, int V, bool kBackward>
+__global__ void __launch_bounds__(kWideThreads)
+bn_wide_reduce_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T* __restrict__ y, long long rows,
+                      int channels, const float* __restrict__ mean, const float* __restrict__ invstd, int relu,
+                      float* __restrict__ partials) {
+    extern __shared__ __align__(16) float s_wide[];
+    float* s_buf = s_wide;                              // [kWideThreads][2V]
+    float* s_part = s_wide + kWideThreads * 2 * V;      // [2][channels]
+    cg::cluster_group cluster = cg::this_cluster();
+    const int cv = channels / V;
+    const int vec = threadIdx.x % cv, my_r = threadIdx.x / cv;
+    const int rows_per_iter = kWideThreads / cv;
+    const long long chunk = (rows + gridDim.x - 1) / gridDim.x;
+    const long long r0 = chunk * blockIdx.x, r1 = r0 + chunk < rows ? r0 + chunk : rows;
+    float a[V], b[V], mu[V], is[V];
+#pragma unroll
+    for (int i = 0; i < V; ++i) { a[i] = 0.f; b[i] = 0.f; mu[i] = 0.f; is[i] = 0.f; }
+    if (kBackward) {
+#pragma unroll
+        for (int i = 0; i < V; ++i) { mu[i] = mean[vec * V + i]; is[i] = invstd[vec * V + i]; }
+    }
+    if (my_r < rows_per_iter) {
+#pragma unroll 4
+        for (long long r = r0 + my_r; r < r1; r += rows_per_iter) {
+            const long long off = r * channels + vec * V;
+            float xv[V];
+            Vec<T, V>::load(x + off, xv);
+            if (kBackward) {
+                float g[V];
+                Vec<T, V>::load(dy + off, g);
+                if (relu) {
+                    float yv[V];
+                    Vec<T, V>::load(y + off, yv);
+#pragma unroll
+                    for (int i = 0; i < V; ++i) g[i] = yv[i] > 0.f ? g[i] : 0.f;
+                }
+#pragma unroll
+                for (int i = 0; i < V; ++i) { a[i] += g[i]; b[i] += g[i] * (xv[i] - mu[i]) * is[i]; }
+            } else {
+#pragma unroll
+                for (int i = 0; i < V; ++i) { a[i] += xv[i]; b[i] += xv[i] * xv[i]; }
+            }
+        }
+    }
+    wide_block_fold<V>(cv, a, b, s_buf, s_part, channels);
+    cluster.sync();
+    if (cluster.block_rank() == 0) {
+        const unsigned int size = cluster.num_blocks();
+        float* out = partials + (size_t)(blockIdx.x / size) * 2 * channels;
+        for (int j = threadIdx.x; j < 2 * channels; j += kWideThreads) {
+            float acc = 0.f;
+            for (unsigned int r = 0; r < size; ++r) acc += cluster.map_shared_rank(s_part, r)[j];
+            out[j] = acc;
+        }
+    }
+    cluster.sync();
+}
+
+template <typename T, int V, bool kBackward>
+__global__ void __launch_bounds__(kWideThreads)
+bn_wide_apply_kernel(const T* __restrict__ x, const T* __restrict__ aux, const T* __restrict__ y_or_res,
+                     long long rows, int channels, const float* __restrict__ gamma, const float* __restrict__ beta,
+                     float eps, int relu, const float* __restrict__ partials, int n_partials,
+                     float* __restrict__ mean, float* __restrict__ invstd, float* __restrict__ dgamma,
+                     float* __restrict__ dbeta, T* __restrict__ out, T* __restrict__ dresidual) {
+    // forward : x = input, y_or_res = residual (may be null), out = y; writes mean / invstd
+    // backward: x = input, aux = dy, y_or_res = forward output (ReLU mask), out = dx; reads mean /
+    //           invstd, writes dgamma / dbeta
+    extern __shared__ __align__(16) float s_tab[];  // [2][channels]: fwd scale/shift, bwd a/b
+    float* s_t0 = s_tab;
+    float* s_t1 = s_tab + channels;
+    const float inv_rows = 1.f / (float)rows;
+    for (int c = threadIdx.x; c < channels; c += kWideThreads) {
+        float p0 = 0.f, p1 = 0.f;
+        for (int k = 0; k < n_partials; ++k) {
+            p0 += partials[(size_t)k * 2 * channels + c];
+            p1 += partials[(size_t)k * 2 * channels + channels + c];
+        }
+        if (!kBackward) {
+            const float mu = p0 * inv_rows;
+            float var = p1 * inv_rows - mu * mu;
+            var = var > 0.f ? var : 0.f;
+            const float is = rsqrtf(var + eps);
+            const float sc = gamma[c] * is;
+            s_t0[c] = sc;
+            s_t1[c] = beta[c] - mu * sc;
+            if (blockIdx.x == 0) { mean[c] = mu; invstd[c] = is; }
+        } else {
+            s_t0[c] = p0 * inv_rows;
+            s_t1[c] = p1 * inv_rows;
+            if (blockIdx.x == 0) { dbeta[c] = p0; dgamma[c] = p1; }
+        }
+    }
+    __syncthreads();
+    const int cv = channels / V;
+    const int vec = threadIdx.x % cv, my_r = threadIdx.x / cv;
+    const int rows_per_iter = kWideThreads / cv;
+    if (my_r >= rows_per_iter) return;
+    float t0[V], t1[V], mu[V], is[V], k[V];
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+        const int c = vec * V + i;
+        t0[i] = s_t0[c]; t1[i] = s_t1[c];
+        mu[i] = 0.f; is[i] = 0.f; k[i] = 0.f;
+        if (kBackward) { mu[i] = mean[c]; is[i] = invstd[c]; k[i] = gamma[c] * is[i]; }
+    }
+    const long long stride = (long long)gridDim.x * rows_per_iter;
+#pragma unroll 2
+    for (long long r = (long long)blockIdx.x * rows_per_iter + my_r; r < rows; r += stride) {
+        const long long off = r * channels + vec * V;
+        float v[V];
+        Vec<T, V>::load(x + off, v);
+        if (!kBackward) {
+            if (y_or_res != nullptr) {
+                float z[V];
+                Vec<T, V>::load(y_or_res + off, z);
+#pragma unroll
+                for (int i = 0; i < V; ++i) v[i] = fmaf(v[i], t0[i], t1[i]) + z[i];
+            } else {
+#pragma unroll
+                for (int i = 0; i < V; ++i) v[i] = fmaf(v[i], t0[i], t1[i]);
+            }
+            if (relu) {
+#pragma unroll
+                for (int i = 0; i < V; ++i) v[i] = fmaxf(v[i], 0.f);
+            }
+            Vec<T, V>::store(out + off, v);
+        } else {
+            float g[V];
+            Vec<T, V>::load(aux + off, g);
+            if (relu) {
+                float yv[V];
+                Vec<T, V>::load(y_or_res + off, yv);
+#pragma unroll
+                for (int i = 0; i < V; ++i) g[i] = yv[i] > 0.f ? g[i] : 0.f;
+            }
+            if (dresidual != nullptr) Vec<T, V>::store(dresidual + off, g);
+#pragma unroll
+            for (int i = 0; i < V; ++i) {
+                const float xh = (v[i] - mu[i]) * is[i];
+                g[i] = k[i] * (g[i] - t0[i] - xh * t1[i]);
+            }
+            Vec<T, V>::store(out + off, g);
+        }
+    }
+}
+
+// wide path applies when rows are plentiful and a row is at most 512 channel vectors wide
+static bool bn_use_wide(long long rows, int channels, int v) {
+    static const bool disabled = [] { const char* e = getenv("DLS_BN_WIDE"); return e && e[0] == '0'; }();
+    const int cv = channels / v;
+    return !disabled && cv <= kWideThreads && (kWideThreads % cv) == 0 && rows >= 8192 && cv <= 32;
+}
+static int bn_wide_clusters(long long rows, int channels, int v) {
+    const int rows_per_iter = kWideThreads / (channels / v);
+    long long want = rows / ((long long)rows_per_iter * kWideCluster * 4);  // >= 4 rows per thread
+    if (want > kWideMaxClusters) want = kWideMaxClusters;
+    if (want * kWideCluster > 2 * kNumSMs) want = 2 * kNumSMs / kWideCluster;
+    return want < 1 ? 1 : (int)want;
+}
+
+template <typename K, typename... Args>
+static cudaError_t wide_launch(K kernel, int grid, int cluster, size_t smem, cudaStream_t stream, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(kWideThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)cluster;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, args...);
+}
+
+template <typename T, int V>
+static cudaError_t bn_wide_fwd(const void* x, long long rows, int channels, const float* gamma, const float* beta,
+                               const void* residual, float eps, int relu, void* y, float* mean, float* invstd,
+                               float* scratch, cudaStream_t s) {
+    const int clusters = bn_wide_clusters(rows, channels, V);
+    const size_t smem1 = (size_t)(kWideThreads * 2 * V + 2 * channels) * sizeof(float);
+    cudaError_t e = wide_launch(bn_wide_reduce_kernel<T, V, false>, clusters * kWideCluster, kWideCluster, smem1, s,
+                                (const T*)x, (const T*)nullptr, (const T*)nullptr, rows, channels,
+                                (const float*)nullptr, (const float*)nullptr, 0, scratch);
+    if (e != cudaSuccess) return e;
+    g_launch_count.fetch_add(1);
+    const int grid2 = (int)((rows + (kWideThreads / (channels / V)) * 4 - 1) / ((kWideThreads / (channels / V)) * 4));
+    return wide_launch(bn_wide_apply_kernel<T, V, false>, grid2 > 2 * kNumSMs ? 2 * kNumSMs : grid2, 1,
+                       (size_t)2 * channels * sizeof(float), s, (const T*)x, (const T*)nullptr, (const T*)residual,
+                       rows, channels, gamma, beta, eps, relu, (const float*)scratch, clusters, mean, invstd,
+                       (float*)nullptr, (float*)nullptr, (T*)y, (T*)nullptr);
+}
+
+template <typename T, int V>
+static cudaError_t bn_wide_bwd(const void* dy, const void* y, const void* x, long long rows, int channels,
+                               const float* gamma, const float* mean, const float* invstd, int relu, void* dx,
+                               void* dresidual, float* dgamma, float* dbeta, float* scratch, cudaStream_t s) {
+    const int clusters = bn_wide_clusters(rows, channels, V);
+    const size_t smem1 = (size_t)(kWideThreads * 2 * V + 2 * channels) * sizeof(float);
+    cudaError_t e = wide_launch(bn_wide_reduce_kernel<T, V, true>, clusters * kWideCluster, kWideCluster, smem1, s,
+                                (const T*)x, (const T*)dy, (const T*)y, rows, channels, mean, invstd, relu, scratch);
+    if (e != cudaSuccess) return e;
+    g_launch_count.fetch_add(1);
+    const int grid2 = (int)((rows + (kWideThreads / (channels / V)) * 4 - 1) / ((kWideThreads / (channels / V)) * 4));
+    return wide_launch(bn_wide_apply_kernel<T, V, true>, grid2 > 2 * kNumSMs ? 2 * kNumSMs : grid2, 1,
+                       (size_t)2 * channels * sizeof(float), s, (const T*)x, (const T*)dy, (const T*)y, rows,
+                       channels, gamma, (const float*)nullptr, 0.f, relu, (const float*)scratch, clusters,
+                       const_cast<float*>(mean), const_cast<float*>(invstd), dgamma, dbeta, (T*)dx, (T*)dresidual);
+}
+
 struct BnPlan { int v, w, groups, cluster; long long iters; int vec_bytes; };
 constexpr size_t kBnMaxDynSmem = 200 * 1024;
 
@@ -378,13 +623,28 @@ static cudaError_t bn_launch(K kernel, const BnPlan& p, size_t dyn_smem, cudaStr
 
 using namespace dls;
 
+extern "C" int dls_bn_scratch_floats(long long rows, int channels, int dtype) {
+    BnPlan p;
+    if (bn_plan(rows, channels, dtype, &p)) return -1;
+    return bn_use_wide(rows, channels, p.v) ? kWideMaxClusters * 2 * channels : 0;
+}
+
 extern "C" int dls_bn_fwd(const void* x, int dtype, long long rows, int channels, const float* gamma,
                           const float* beta, const void* residual, float eps, int relu, void* y, float* mean,
-                          float* invstd, void* stream) {
+                          float* invstd, float* scratch, void* stream) {
     BnPlan p;
     if (int rc = bn_plan(rows, channels, dtype, &p)) return rc;
     cudaStream_t s = (cudaStream_t)stream;
     cudaError_t e;
+    if (bn_use_wide(rows, channels, p.v)) {
+        if (scratch == nullptr) return fail_msg("dls_bn_fwd: this shape needs the scratch buffer");
+        if (dtype == 1 && p.v == 8) e = bn_wide_fwd<__nv_bfloat16, 8>(x, rows, channels, gamma, beta, residual, eps, relu, y, mean, invstd, scratch, s);
+        else if (dtype == 1) e = bn_wide_fwd<__nv_bfloat16, 4>(x, rows, channels, gamma, beta, residual, eps, relu, y, mean, invstd, scratch, s);
+        else e = bn_wide_fwd<float, 4>(x, rows, channels, gamma, beta, residual, eps, relu, y, mean, invstd, scratch, s);
+        if (e != cudaSuccess) return fail("bn_wide_fwd", e);
+        DLS_LAUNCHED("bn_wide_apply_kernel");
+        return 0;
+    }
     // park the CTA's rows in shared memory between the two phases when they fit
     size_t smem = (size_t)p.iters * kBnThreads * p.vec_bytes;
     const int cached = smem <= kBnMaxDynSmem;
@@ -407,12 +667,21 @@ extern "C" int dls_bn_fwd(const void* x, int dtype, long long rows, int channels
 
 extern "C" int dls_bn_bwd(const void* dy, const void* y, const void* x, int dtype, long long rows, int channels,
                           const float* gamma, const float* mean, const float* invstd, int relu, void* dx,
-                          void* dresidual, float* dgamma, float* dbeta, void* stream) {
+                          void* dresidual, float* dgamma, float* dbeta, float* scratch, void* stream) {
     BnPlan p;
     if (int rc = bn_plan(rows, channels, dtype, &p)) return rc;
     if (relu && y == nullptr) return fail_msg("bn bwd: the forward output is needed for the ReLU mask");
     cudaStream_t s = (cudaStream_t)stream;
     cudaError_t e;
+    if (bn_use_wide(rows, channels, p.v)) {
+        if (scratch == nullptr) return fail_msg("dls_bn_bwd: this shape needs the scratch buffer");
+        if (dtype == 1 && p.v == 8) e = bn_wide_bwd<__nv_bfloat16, 8>(dy, y, x, rows, channels, gamma, mean, invstd, relu, dx, dresidual, dgamma, dbeta, scratch, s);
+        else if (dtype == 1) e = bn_wide_bwd<__nv_bfloat16, 4>(dy, y, x, rows, channels, gamma, mean, invstd, relu, dx, dresidual, dgamma, dbeta, scratch, s);
+        else e = bn_wide_bwd<float, 4>(dy, y, x, rows, channels, gamma, mean, invstd, relu, dx, dresidual, dgamma, dbeta, scratch, s);
+        if (e != cudaSuccess) return fail("bn_wide_bwd", e);
+        DLS_LAUNCHED("bn_wide_apply_kernel");
+        return 0;
+    }
     size_t smem = (size_t)p.iters * kBnThreads * p.vec_bytes * 2;  // masked dy and x
     const int cached = smem <= kBnMaxDynSmem;
     if (!cached) smem = 0;

@@ -35,6 +35,12 @@ def can_fuse(bn: nn.Module, x: torch.Tensor, residual: torch.Tensor | None) -> b
     return True
 
 
+def _scratch(rows: int, channels: int, dtype: int, device: torch.device) -> torch.Tensor | None:
+    """Per-call partial-sum buffer of the row-major path (a fresh tensor: safe under graph capture)."""
+    need = runtime.require().dls_bn_scratch_floats(rows, channels, dtype)
+    return torch.empty(need, dtype=torch.float32, device=device) if need > 0 else None
+
+
 class _FusedBNAct(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, bias, residual, eps, relu, bn):
@@ -44,9 +50,10 @@ class _FusedBNAct(torch.autograd.Function):
         y = torch.empty_like(x)  # preserves channels-last
         mean = torch.empty(c, dtype=torch.float32, device=x.device)
         invstd = torch.empty(c, dtype=torch.float32, device=x.device)
+        scratch = _scratch(rows, c, dtype, x.device)
         runtime.call("dls_bn_fwd", x.data_ptr(), dtype, rows, c, weight.data_ptr(), bias.data_ptr(),
                      runtime.ptr(residual), float(eps), int(relu), y.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
-                     runtime.stream_ptr(x.device))
+                     runtime.ptr(scratch), runtime.stream_ptr(x.device))
         STATS["fused_fwd"] += 1
         ctx.save_for_backward(x, y if relu else x, weight, mean, invstd)
         ctx.relu, ctx.has_residual, ctx.bn = bool(relu), residual is not None, bn
@@ -64,9 +71,10 @@ class _FusedBNAct(torch.autograd.Function):
         dres = torch.empty_like(x) if ctx.has_residual else None
         dgamma = torch.empty(c, dtype=torch.float32, device=x.device)
         dbeta = torch.empty(c, dtype=torch.float32, device=x.device)
+        scratch = _scratch(rows, c, dtype, x.device)
         runtime.call("dls_bn_bwd", dy.data_ptr(), y.data_ptr(), x.data_ptr(), dtype, rows, c, weight.data_ptr(),
                      mean.data_ptr(), invstd.data_ptr(), int(ctx.relu), dx.data_ptr(), runtime.ptr(dres),
-                     dgamma.data_ptr(), dbeta.data_ptr(), runtime.stream_ptr(x.device))
+                     dgamma.data_ptr(), dbeta.data_ptr(), runtime.ptr(scratch), runtime.stream_ptr(x.device))
         return dx, dgamma, dbeta, dres, None, None, None
 
 

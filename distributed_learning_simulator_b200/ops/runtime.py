@@ -51,10 +51,11 @@ _SIGNATURES = {
     "dls_copy_device": [c_void_p, c_void_p, c_ll, c_void_p],
     "dls_gemm_bf16_tn": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                          c_void_p],
+    "dls_bn_scratch_floats": [c_ll, c_int, c_int],
     "dls_bn_fwd": [c_void_p, c_int, c_ll, c_int, c_void_p, c_void_p, c_void_p, c_float, c_int, c_void_p, c_void_p,
-                   c_void_p, c_void_p],
+                   c_void_p, c_void_p, c_void_p],
     "dls_bn_bwd": [c_void_p, c_void_p, c_void_p, c_int, c_ll, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p,
-                   c_void_p, c_void_p, c_void_p, c_void_p],
+                   c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
     "dls_sign_pack": [c_void_p, c_ll, c_void_p, c_void_p],
     "dls_sign_majority": [c_void_p, c_int, c_ll, c_void_p, c_void_p],
     "dls_dropout_mask": [c_void_p, c_ll, c_float, c_u64, c_void_p, c_void_p, c_void_p],

@@ -87,14 +87,18 @@ int dls_metric_accumulate(const float* logits, const long long* targets, const f
  *      (reference: BatchNorm/ReLU inside the external Trainer's model forward/backward;
  *      batch statistics are always used, simulation_lib/util/model.py:23) ---------------------
  * x/y/residual/dy/dx: [rows, channels] with channels contiguous (NHWC), dtype 0 = fp32,
- * 1 = bf16; channels % 4 == 0.  One cluster launch each way: the CTAs that share a channel
- * group combine their statistics through distributed shared memory.  fwd writes mean/invstd
- * (fp32 [channels]) for bwd; bwd writes dgamma/dbeta (fp32 [channels]). */
+ * 1 = bf16; channels % 4 == 0.  Few rows / many channels: one cluster launch each way, the CTAs
+ * that share a channel group combine their statistics through distributed shared memory.  Many
+ * rows / few channels: a row-major reduce launch (cluster DSMEM fold, one partial per cluster in
+ * `scratch`) plus an elementwise launch.  scratch: dls_bn_scratch_floats() floats (0 = not needed,
+ * NULL allowed).  fwd writes mean/invstd (fp32 [channels]) for bwd; bwd writes dgamma/dbeta. */
+int dls_bn_scratch_floats(long long rows, int channels, int dtype);
 int dls_bn_fwd(const void* x, int dtype, long long rows, int channels, const float* gamma, const float* beta,
-               const void* residual, float eps, int relu, void* y, float* mean, float* invstd, void* stream);
+               const void* residual, float eps, int relu, void* y, float* mean, float* invstd, float* scratch,
+               void* stream);
 int dls_bn_bwd(const void* dy, const void* y, const void* x, int dtype, long long rows, int channels,
                const float* gamma, const float* mean, const float* invstd, int relu, void* dx, void* dresidual,
-               float* dgamma, float* dbeta, void* stream);
+               float* dgamma, float* dbeta, float* scratch, void* stream);
 
 /* ---- bf16 GEMM on tcgen05 tensor cores, TMEM accumulators, TMA operand loads ------------
  *      (reference: torch.nn.Linear inside the external Inferencer, server/server.py:40-55, and
