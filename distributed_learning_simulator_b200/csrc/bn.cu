@@ -338,7 +338,7 @@ __device__ __forceinline__ void wide_block_fold(int cv, const float (&a)[V], con
         s_buf[threadIdx.x * 2 * V + V + i] = b[i];
     }
     __syncthreads();
-    const int rows_in_block = kWideThreads / cv;
+    const int rows_in_block = kWideThreads / cv;  // threads past rows_in_block * cv are idle (zeros)
     for (int j = threadIdx.x; j < cv * 2 * V; j += kWideThreads) {
         const int vec = j / (2 * V), k = j % (2 * V);
         float acc = 0.f;
@@ -495,11 +495,12 @@ bn_wide_apply_kernel(const T* __restrict__ x, const T* __restrict__ aux, const T
     }
 }
 
-// wide path applies when rows are plentiful and a row is at most 512 channel vectors wide
+// wide path applies when rows are plentiful and a row is at most 128 channel vectors wide (any count:
+// the threads of a CTA that do not fit a whole number of rows stay idle)
 static bool bn_use_wide(long long rows, int channels, int v) {
     static const bool disabled = [] { const char* e = getenv("DLS_BN_WIDE"); return e && e[0] == '0'; }();
     const int cv = channels / v;
-    return !disabled && cv <= kWideThreads && (kWideThreads % cv) == 0 && rows >= 8192 && cv <= 32;
+    return !disabled && cv <= 128 && rows >= 8192;
 }
 static int bn_wide_clusters(long long rows, int channels, int v) {
     const int rows_per_iter = kWideThreads / (channels / v);

@@ -271,7 +271,7 @@ def test_block_sqdiff(dev):
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
-@pytest.mark.parametrize("shape", [(64, 64, 32, 32), (7, 24, 5, 3), (3, 512, 4, 4), (16, 36, 8, 8)])
+@pytest.mark.parametrize("shape", [(64, 64, 32, 32), (7, 24, 5, 3), (3, 512, 4, 4), (16, 36, 8, 8), (16, 36, 32, 32)])
 @pytest.mark.parametrize("relu,with_res", [(True, False), (True, True), (False, False)])
 def test_fused_bn_act_matches_pytorch(dev, dtype, shape, relu, with_res):
     from distributed_learning_simulator_b200.ops import bn as B
