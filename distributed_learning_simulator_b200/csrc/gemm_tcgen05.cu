@@ -5,16 +5,18 @@
 // (reference path: one CPU model average + one full eager test inference per coalition,
 // simulation_lib/method/shapley_value/shapley_value_algorithm.py:67-76).
 //
-// Structure (sm_100a, one CTA per 128 x 64 output tile, no library GEMM):
-//   warp 0      TMA producer: cp.async.bulk.tensor loads of the A (128 x 64) and B (64 x 64)
+// Structure (sm_100a, one CTA per 128 x {64,128,256} output tile, no library GEMM):
+//   warp 0      TMA producer: cp.async.bulk.tensor loads of the A (128 x 64) and B (BLOCK_N x 64)
 //               K-slices into a 4-stage 128B-swizzled shared-memory ring, mbarrier complete_tx
-//   warp 1      allocates TMEM, then one lane issues tcgen05.mma (M128 N64 K16, bf16 -> fp32
+//   warp 1      allocates TMEM, then one lane issues tcgen05.mma (M128 N64/128/256 K16, bf16 -> fp32
 //               accumulators in tensor memory); tcgen05.commit releases ring slots and finally
 //               signals the epilogue
 //   warps 2-5   epilogue: tcgen05.ld (32 lanes x 32 columns per instruction) -> bias / ReLU ->
 //               global stores (fp32 or bf16)
 // Out-of-range rows/columns/K are zero-filled by the TMA unit, so any M, N and any K % 8 == 0
 // work without padding copies.
+#include <stdlib.h>
+
 #include <cuda.h>
 #include <cuda_bf16.h>
 
@@ -24,14 +26,12 @@
 namespace dls {
 
 constexpr int kGemmBlockM = 128;
-constexpr int kGemmBlockN = 64;
+// BLOCK_N is a template parameter: 64, 128 or 256 columns per tile (= TMEM columns)
 constexpr int kGemmBlockK = 64;   // 64 bf16 = 128 bytes = one swizzle atom row
 constexpr int kGemmUmmaK = 16;
 constexpr int kGemmStages = 4;
 constexpr int kGemmThreads = 192;
 constexpr uint32_t kBytesA = kGemmBlockM * kGemmBlockK * 2;
-constexpr uint32_t kBytesB = kGemmBlockN * kGemmBlockK * 2;
-constexpr uint32_t kTmemCols = 64;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -78,13 +78,14 @@ __device__ __forceinline__ uint64_t umma_smem_desc(uint32_t smem_addr) {
     return desc;
 }
 
-// kind::f16 instruction descriptor: D = fp32, A = B = bf16, both K-major, M = 128, N = 64
+// kind::f16 instruction descriptor: D = fp32, A = B = bf16, both K-major, M = 128, N = kBlockN
+template <int kBlockN>
 __device__ __forceinline__ uint32_t umma_instr_desc() {
     uint32_t d = 0;
     d |= 1u << 4;                         // c_format: F32
     d |= 1u << 7;                         // a_format: BF16
     d |= 1u << 10;                        // b_format: BF16
-    d |= (uint32_t)(kGemmBlockN >> 3) << 17;  // n_dim
+    d |= (uint32_t)(kBlockN >> 3) << 17;  // n_dim
     d |= (uint32_t)(kGemmBlockM >> 4) << 24;  // m_dim
     return d;
 }
@@ -103,24 +104,29 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
                  : "memory");
 }
 
+template <int kBlockN>
 struct __align__(1024) GemmSmem {
     __nv_bfloat16 a[kGemmStages][kGemmBlockM * kGemmBlockK];
-    __nv_bfloat16 b[kGemmStages][kGemmBlockN * kGemmBlockK];
+    __nv_bfloat16 b[kGemmStages][kBlockN * kGemmBlockK];
     uint64_t full[kGemmStages];
     uint64_t empty[kGemmStages];
     uint64_t tmem_full;
     uint32_t tmem_base;
 };
 
+template <int kBlockN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                          const float* __restrict__ bias, long long bias_batch_stride, void* __restrict__ c,
                          int out_bf16, int m, int n, int k, int b_shared, int relu) {
     extern __shared__ unsigned char smem_raw[];
-    GemmSmem& sm = *reinterpret_cast<GemmSmem*>(
+    constexpr uint32_t kBytesB = kBlockN * kGemmBlockK * 2;
+    constexpr uint32_t kTmemCols = kBlockN;
+    using Smem = GemmSmem<kBlockN>;
+    Smem& sm = *reinterpret_cast<Smem*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int m0 = blockIdx.x * kGemmBlockM, n0 = blockIdx.y * kGemmBlockN, batch = blockIdx.z;
+    const int m0 = blockIdx.x * kGemmBlockM, n0 = blockIdx.y * kBlockN, batch = blockIdx.z;
     const int num_kb = (k + kGemmBlockK - 1) / kGemmBlockK;
 
     if (warp == 0 && lane == 0) {
@@ -157,7 +163,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
         }
     } else if (warp == 1) {
         if (lane == 0) {  // ---- MMA issuer
-            const uint32_t idesc = umma_instr_desc();
+            const uint32_t idesc = umma_instr_desc<kBlockN>();
             for (int kb = 0; kb < num_kb; ++kb) {
                 const int s = kb % kGemmStages;
                 const uint32_t phase = (kb / kGemmStages) & 1;
@@ -182,7 +188,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const float* bias_b = bias != nullptr ? bias + (long long)batch * bias_batch_stride : nullptr;
 #pragma unroll
-        for (int chunk = 0; chunk < kGemmBlockN / 32; ++chunk) {
+        for (int chunk = 0; chunk < kBlockN / 32; ++chunk) {
             uint32_t r[32];
             const uint32_t taddr = tmem_acc + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(chunk * 32);
             asm volatile(
@@ -200,15 +206,41 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
             if (row < m) {
                 const int col0 = n0 + chunk * 32;
                 const long long out_off = ((long long)batch * m + row) * n + col0;
+                float v[32];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
-                    const int col = col0 + j;
-                    if (col < n) {
-                        float v = __uint_as_float(r[j]);
-                        if (bias_b != nullptr) v += bias_b[col];
-                        if (relu) v = fmaxf(v, 0.f);
-                        if (out_bf16) reinterpret_cast<__nv_bfloat16*>(c)[out_off + j] = __float2bfloat16(v);
-                        else reinterpret_cast<float*>(c)[out_off + j] = v;
+                    v[j] = __uint_as_float(r[j]);
+                    if (bias_b != nullptr && col0 + j < n) v[j] += bias_b[col0 + j];
+                    if (relu) v[j] = fmaxf(v[j], 0.f);
+                }
+                const bool full = col0 + 32 <= n;
+                if (out_bf16) {
+                    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(c) + out_off;
+                    if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+                        // 32 columns = 64 bytes: four 128-bit stores of packed bf16 pairs
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            uint4 pk;
+                            __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) h[e] = __floats2bfloat162_rn(v[8 * q + 2 * e], v[8 * q + 2 * e + 1]);
+                            reinterpret_cast<uint4*>(dst)[q] = pk;
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (col0 + j < n) dst[j] = __float2bfloat16(v[j]);
+                    }
+                } else {
+                    float* dst = reinterpret_cast<float*>(c) + out_off;
+                    if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+                        for (int q = 0; q < 8; ++q)
+                            reinterpret_cast<float4*>(dst)[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (col0 + j < n) dst[j] = v[j];
                     }
                 }
             }
@@ -269,16 +301,34 @@ extern "C" int dls_gemm_bf16_tn(const void* a, const void* b, const float* bias,
     if (batch > 65535) return fail_msg("dls_gemm_bf16_tn: batch too large");
     CUtensorMap map_a, map_b;
     if (int rc = make_map(&map_a, a, m, k, batch, kGemmBlockM)) return rc;
-    if (int rc = make_map(&map_b, b, n, k, b_shared ? 1 : batch, kGemmBlockN)) return rc;
-    const size_t smem = sizeof(GemmSmem) + 1024;
-    static thread_local bool configured = false;
-    if (!configured) {
-        DLS_CHECK(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = true;
-    }
-    dim3 grid((m + kGemmBlockM - 1) / kGemmBlockM, (n + kGemmBlockN - 1) / kGemmBlockN, batch);
-    gemm_bf16_tcgen05_kernel<<<grid, kGemmThreads, smem, (cudaStream_t)stream>>>(
-        map_a, map_b, bias, b_shared ? 0 : (long long)n, c, out_dtype, m, n, k, b_shared, relu);
+    // tile width: narrow outputs keep a narrow tile; wide ones take 256 columns when that still
+    // leaves at least one wave of CTAs
+    const long long m_tiles = (m + kGemmBlockM - 1) / kGemmBlockM;
+    int block_n = 64;
+    if (n > 128 && m_tiles * ((n + 255) / 256) * batch >= kNumSMs) block_n = 256;
+    else if (n > 64) block_n = 128;
+    static const int forced = [] { const char* e = getenv("DLS_GEMM_BN"); return e ? atoi(e) : 0; }();  // tuning knob
+    if ((forced == 64 || forced == 128 || forced == 256) && n > forced / 2) block_n = forced;
+    if (int rc = make_map(&map_b, b, n, k, b_shared ? 1 : batch, block_n)) return rc;
+    dim3 grid((unsigned)m_tiles, (n + block_n - 1) / block_n, batch);
+    const long long bias_stride = b_shared ? 0 : (long long)n;
+    cudaStream_t s = (cudaStream_t)stream;
+#define DLS_GEMM_LAUNCH(BN)                                                                                   \
+    do {                                                                                                      \
+        const size_t smem = sizeof(GemmSmem<BN>) + 1024;                                                      \
+        static thread_local bool configured = false;                                                          \
+        if (!configured) {                                                                                    \
+            DLS_CHECK(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                           (int)smem));                                                       \
+            configured = true;                                                                                \
+        }                                                                                                     \
+        gemm_bf16_tcgen05_kernel<BN><<<grid, kGemmThreads, smem, s>>>(map_a, map_b, bias, bias_stride, c, out_dtype, \
+                                                                      m, n, k, b_shared, relu);               \
+    } while (0)
+    if (block_n == 256) DLS_GEMM_LAUNCH(256);
+    else if (block_n == 128) DLS_GEMM_LAUNCH(128);
+    else DLS_GEMM_LAUNCH(64);
+#undef DLS_GEMM_LAUNCH
     DLS_LAUNCHED("gemm_bf16_tcgen05_kernel");
     return 0;
 }

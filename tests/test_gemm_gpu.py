@@ -5,7 +5,8 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("m,n,k", [(128, 64, 64), (200, 10, 88), (5000, 120, 400), (37, 130, 1024), (1, 84, 120)])
+@pytest.mark.parametrize("m,n,k", [(128, 64, 64), (200, 10, 88), (5000, 120, 400), (37, 130, 1024), (1, 84, 120),
+                                   (8192, 700, 256), (300, 300, 264)])
 @pytest.mark.parametrize("bias,relu", [(False, False), (True, True)])
 def test_linear_bf16(m, n, k, bias, relu):
     from distributed_learning_simulator_b200.ops import gemm as G
