@@ -16,6 +16,8 @@ class SignSGDServer(Server):
         kwargs.pop("algorithm", None)
         super().__init__(**kwargs)
         self.algorithm = None
+        if hasattr(self._endpoint.topology, "partial_exchange"):
+            self._endpoint.topology.partial_exchange = True  # workers report at different times
         self.__gradients: dict[int, Message] = {}
         self.__epoch_reports: dict[int, Message] = {}
         self.__finished: set[int] = set()

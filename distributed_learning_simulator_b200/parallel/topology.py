@@ -39,6 +39,11 @@ class DistributedTopology(ThreadCentralTopology):
         self.local_workers = [w for w in range(worker_num) if ctx.is_local(w)]
         self._inbox: dict[int, Any] = {}
         self.exchanges = 0
+        # False (default): every worker reports once per exchange (aggregation servers) -- a replica
+        # blocks until all of its local workers have data, then swaps.  True: workers may report at
+        # different times (per-step protocols such as sign_SGD) -- replicas swap whatever is there,
+        # polling every few milliseconds while nothing is.
+        self.partial_exchange = False
 
     def is_local(self, worker_id: int) -> bool:
         return self.ctx.is_local(worker_id)
@@ -106,6 +111,8 @@ class DistributedTopology(ThreadCentralTopology):
         if have:
             return have
         local_needed = sorted(w for w in worker_ids if self.is_local(w))
+        if self.partial_exchange:
+            return self._partial_wait(worker_ids, local_needed, timeout)
         local_msgs: dict[int, Any] = {}
         for w in local_needed:
             ready = super().server_wait({w}, timeout)
@@ -121,6 +128,30 @@ class DistributedTopology(ThreadCentralTopology):
             for w, obj in part.items():
                 self._inbox[w] = local_msgs[w] if rank == self.ctx.rank else self._decode(obj)
         return {w for w in worker_ids if w in self._inbox}
+
+    def _partial_wait(self, worker_ids: set[int], local_needed: list[int], timeout: float | None) -> set[int]:
+        import time
+
+        deadline = None if timeout is None else time.monotonic() + timeout
+        while True:
+            ready = super().server_wait(set(local_needed), 0.003) if local_needed else set()
+            if not local_needed:
+                time.sleep(0.003)
+            local_msgs = {w: super().server_get(w) for w in sorted(ready)}
+            wire: dict[int, Any] = {}
+            for w, msg in local_msgs.items():
+                wire[w], local_msgs[w] = self._encode(w, msg)
+            gathered = self.ctx.exchange(wire)
+            self.exchanges += 1
+            for rank, part in enumerate(gathered):
+                for w, obj in part.items():
+                    self._inbox[w] = local_msgs[w] if rank == self.ctx.rank else self._decode(obj)
+            have = {w for w in worker_ids if w in self._inbox}
+            # every replica sees the same inbox, so they all leave the loop in the same iteration
+            if have:
+                return have
+            if deadline is not None and time.monotonic() > deadline:
+                return set()
 
     def server_send(self, worker_id: int, data: Any) -> None:
         if self.is_local(worker_id):

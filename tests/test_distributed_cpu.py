@@ -41,7 +41,7 @@ def _run(tmp_path, conf, world):
     else:
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
                "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), str(script)]
-    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=300)
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     return [json.load(open(out / f"rank_{r}.json")) for r in range(world)]
 
@@ -63,3 +63,50 @@ def test_two_ranks_agree_with_single_process(tmp_path):
         assert abs(a["test_loss"] - b["test_loss"]) < 1e-4
     server_dir = os.path.join(two[0]["save_dir"], "server")
     assert os.path.isfile(os.path.join(server_dir, "round_record.json"))
+
+
+
+MULTI_SCRIPT = r"""
+import json, os, sys
+sys.path.insert(0, {root!r})
+from distributed_learning_simulator_b200 import load_config_from_dict, train
+from distributed_learning_simulator_b200.training import get_last_training_result
+results = {{}}
+for name, conf in {confs!r}.items():
+    train(load_config_from_dict(conf))
+    res = get_last_training_result()
+    results[name] = {{str(k): v for k, v in res["performance"].items()}}
+with open(os.path.join({out!r}, "multi_%s.json" % os.environ.get("RANK", "0")), "w") as f:
+    json.dump(results, f)
+"""
+
+_TINY = {"optimizer_name": "SGD", "learning_rate_scheduler_name": "CosineAnnealingLR", "batch_size": 32, "round": 2,
+         "epoch": 1, "learning_rate": 0.05, "dataset_name": "MNIST", "model_name": "LeNet5", "worker_number": 4,
+         "dataset_kwargs": {"train_size": 480, "test_size": 160}}
+
+_METHODS = {
+    "fed_obd": {"endpoint_kwargs": {"server": {"weight": 0.01}, "worker": {"weight": 0.01}},
+                "algorithm_kwargs": {"dropout_rate": 0.5, "random_client_number": 3, "second_phase_epoch": 1}},
+    "fed_paq": {"algorithm_kwargs": {"random_client_number": 3}},
+    "GTG_shapley_value": {"worker_number": 3},
+    "sign_SGD": {"round": 1, "distribute_init_parameters": False, "learning_rate": 0.01},
+    "fed_gnn": {"dataset_name": "Cora", "model_name": "TwoGCN",
+                "dataset_kwargs": {"num_nodes": 240, "features": 16, "classes": 3},
+                "algorithm_kwargs": {"share_feature": True, "batch_number": 2}},
+}
+
+
+def test_methods_under_two_ranks(tmp_path):
+    """Every method family also runs with one process per device (one launch, run back to back):
+    the replicated servers agree on every recorded metric."""
+    confs = {name: {**_TINY, **extra, "distributed_algorithm": name} for name, extra in _METHODS.items()}
+    script = tmp_path / "multi.py"
+    script.write_text(MULTI_SCRIPT.format(root=ROOT, confs=confs, out=str(tmp_path)))
+    env = dict(os.environ, DLS_FORCE_CPU="1", DLS_OUTPUT_ROOT=str(tmp_path), OMP_NUM_THREADS="2")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), str(script)]
+    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=420)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    r0, r1 = (json.load(open(tmp_path / f"multi_{r}.json")) for r in range(2))
+    assert r0 == r1 and set(r0) == set(_METHODS)
+    assert all(len(perf) >= 1 for perf in r0.values())
