@@ -8,10 +8,12 @@ together:
 
 1. coalition models ``W_s = sum_i r_i^s W_i`` are built by the fused reduce kernel straight
    into one ``[S, P]`` buffer (no per-coalition tensors, no host round trip);
-2. the test set runs through all S models at once: the convolutions see the coalitions as
-   extra output channels / groups, the fully connected layers are ONE batched launch each of
-   the hand-written tcgen05 GEMM (``ops.gemm.linear_bf16`` with batch = coalition, bias and
-   ReLU fused in its epilogue);
+2. the test set runs through all S models at once, every matrix product on the hand-written
+   tcgen05 GEMM (``ops.gemm.linear_bf16``, bias and ReLU fused in its epilogue): conv1 is ONE GEMM
+   whose B operand stacks the first-layer filters of all coalitions (the image patches are shared,
+   so the coalition models are never materialised as separate convolutions), conv2 and the three
+   fully connected layers are one batched launch each with batch = coalition; patch extraction
+   (unfold) and pooling stay in PyTorch;
 3. per-coalition accuracy / loss are reduced on the device and read back once.
 
 The GTG engine's truncation rules are applied afterwards to decide which utilities are
@@ -98,12 +100,34 @@ class _LeNet5BatchEvaluator:
             fw = [p[f"fc{j}.weight"].to(torch.bfloat16).contiguous() for j in (1, 2, 3)]
             fb = [p[f"fc{j}.bias"].contiguous() for j in (1, 2, 3)]
             acc = torch.zeros(S, 3, dtype=torch.float64, device=self.device)
+            conv_gemm = bool(self.server.config.algorithm_kwargs.get("subset_eval_conv_gemm", True))
+            if conv_gemm:
+                # convolution weights as GEMM operands: conv1 of ALL coalitions is one B matrix
+                # [S*6, C*k*k] (the image patches are shared), conv2 is one [16, 6*k*k] matrix per coalition
+                k1, k2 = w1.shape[-1], w2.shape[-1]
+                g1 = w1.reshape(S * 6, -1).to(torch.bfloat16).contiguous()
+                g2 = p["conv2.weight"].reshape(S, 16, -1).to(torch.bfloat16).contiguous()
             for batch in tester._loader(phase):
                 x, y = batch.inputs[0], batch.targets
-                h = F.max_pool2d(F.relu(F.conv2d(x, w1, b1, padding=self.pad)), 2)      # [B, S*6, 14, 14]
-                h = F.max_pool2d(F.relu(F.conv2d(h, w2, b2, groups=S)), 2)                 # [B, S*16, 5, 5]
-                B = h.shape[0]
-                feat = h.reshape(B, S, -1).permute(1, 0, 2).to(torch.bfloat16).contiguous()  # [S, B, 400]
+                B = x.shape[0]
+                if conv_gemm:
+                    hw = x.shape[-1] + 2 * self.pad - k1 + 1
+                    cols = F.unfold(x, k1, padding=self.pad).transpose(1, 2).reshape(B * hw * hw, -1)
+                    z = gemm.linear_bf16(cols.to(torch.bfloat16), g1, b1, relu=True, out_dtype=torch.bfloat16)
+                    h = z.view(B, hw, hw, S * 6).permute(0, 3, 1, 2)            # channels-last [B, S*6, 28, 28]
+                    h = F.max_pool2d(h, 2)                                        # [B, S*6, 14, 14]
+                    hw2 = h.shape[-1] - k2 + 1
+                    cols = F.unfold(h.float(), k2)                                 # [B, S*6*k*k, hw2*hw2]
+                    cols = cols.view(B, S, 6 * k2 * k2, hw2 * hw2).permute(1, 0, 3, 2).reshape(S, B * hw2 * hw2, -1)
+                    z = gemm.linear_bf16(cols.to(torch.bfloat16), g2, p["conv2.bias"].contiguous(), relu=True,
+                                         out_dtype=torch.bfloat16)                # [S, B*100, 16]
+                    h = z.view(S, B, hw2, hw2, 16).permute(0, 1, 4, 2, 3).reshape(S * B, 16, hw2, hw2)
+                    h = F.max_pool2d(h.float(), 2)                                # [S*B, 16, 5, 5]
+                    feat = h.reshape(S, B, -1).to(torch.bfloat16).contiguous()    # [S, B, 400] in (c, h, w) order
+                else:
+                    h = F.max_pool2d(F.relu(F.conv2d(x, w1, b1, padding=self.pad)), 2)      # [B, S*6, 14, 14]
+                    h = F.max_pool2d(F.relu(F.conv2d(h, w2, b2, groups=S)), 2)                 # [B, S*16, 5, 5]
+                    feat = h.reshape(B, S, -1).permute(1, 0, 2).to(torch.bfloat16).contiguous()  # [S, B, 400]
                 z = gemm.linear_bf16(feat, fw[0], fb[0], relu=True, out_dtype=torch.bfloat16)
                 z = gemm.linear_bf16(z, fw[1], fb[1], relu=True, out_dtype=torch.bfloat16)
                 logits = gemm.linear_bf16(z, fw[2], fb[2], relu=False, out_dtype=torch.float32)  # [S, B, classes]
