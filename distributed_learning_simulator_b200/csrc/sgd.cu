@@ -38,7 +38,7 @@ sgd_step_kernel(float* __restrict__ params, float* __restrict__ mom, const float
         const bool fast = (i + 4 <= s_off[t + 1]) && ((j & 3) == 0) && grads[t] != nullptr;
         float g[4], p[4], m[4];
         if (fast) {
-            const float4 gv = *reinterpret_cast<const float4*>(grads[t] + j);
+            const float4 gv = ld_stream_f4(grads[t] + j);  // gradients are read exactly once
             const float4 pv = *reinterpret_cast<const float4*>(params + i);
             g[0] = gv.x; g[1] = gv.y; g[2] = gv.z; g[3] = gv.w;
             p[0] = pv.x; p[1] = pv.y; p[2] = pv.z; p[3] = pv.w;
@@ -164,7 +164,7 @@ extern "C" int dls_sgd_step(float* params, float* momentum_buf, const float* con
     if (momentum != 0.f && momentum_buf == nullptr) return fail_msg("dls_sgd_step: momentum buffer missing");
     const size_t smem = (size_t)(n_tensors + 1) * sizeof(long long);
     // grid from the arena size is unknown on the host without a sync: a fixed persistent grid
-    const int grid = kNumSMs * 4;
+    const int grid = kNumSMs * 8;
     sgd_step_kernel<<<grid, kSgdThreads, smem, (cudaStream_t)stream>>>(params, momentum_buf, grads, tensor_offsets,
                                                                          n_tensors, lr_table, lr_len, state,
                                                                          weight_decay, momentum, dampening, nesterov);

@@ -69,6 +69,21 @@ state = torch.tensor([0, 1, 0, 0], dtype=torch.int32, device=dev)
 timed("sgd_step momentum P=11.2M", lambda: S.sgd_step(flat, mom, table, offsets, len(layout.names), lr, state, 1e-4, 0.9),
       bytes_moved=5 * P * 4)
 
+def sgd10():
+    for _ in range(10):
+        S.sgd_step(flat, mom, table, offsets, len(layout.names), lr, state, 1e-4, 0.9)
+
+
+timed("sgd_step x10 back to back (working set 225 MB > L2)", sgd10, bytes_moved=10 * 5 * P * 4, cold=False)
+rows8 = rows
+
+
+def red10():
+    for _ in range(10):
+        R.reduce_rows_f32(rows8, [1.0] * 8, old, 1.0, 0.125, out=out, check_nan=False)
+
+
+timed("fedavg_reduce_f32 K=8 x10 back to back", red10, bytes_moved=10 * (8 + 2) * P * 4, cold=False)
 timed("sq_quant P=11.2M", lambda: Q.sq_quant(flat, layout, 255, seed=1), bytes_moved=P * (4 + 4 + 1 + 0.125))
 q = Q.sq_quant(flat, layout, 255, seed=1)
 deq = torch.empty(P, device=dev)
