@@ -12,7 +12,9 @@
 //               accumulators in tensor memory); tcgen05.commit releases ring slots and finally
 //               signals the epilogue
 //   warps 2-5   epilogue: tcgen05.ld (32 lanes x 32 columns per instruction) -> bias / ReLU ->
-//               global stores (fp32 or bf16)
+//               128-bit global stores (fp32 or bf16)
+// The CTAs are persistent (one per SM, static tile schedule) and the accumulator is double
+// buffered in TMEM, so the epilogue of one tile overlaps the MMAs of the next.
 // Out-of-range rows/columns/K are zero-filled by the TMA unit, so any M, N and any K % 8 == 0
 // work without padding copies.
 #include <stdlib.h>
@@ -110,24 +112,33 @@ struct __align__(1024) GemmSmem {
     __nv_bfloat16 b[kGemmStages][kBlockN * kGemmBlockK];
     uint64_t full[kGemmStages];
     uint64_t empty[kGemmStages];
-    uint64_t tmem_full;
+    uint64_t tmem_full[2];   // accumulator stage ready for the epilogue
+    uint64_t tmem_empty[2];  // accumulator stage drained, the MMA warp may overwrite it
     uint32_t tmem_base;
 };
+
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 
 template <int kBlockN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                          const float* __restrict__ bias, long long bias_batch_stride, void* __restrict__ c,
-                         int out_bf16, int m, int n, int k, int b_shared, int relu) {
+                         int out_bf16, int m, int n, int k, int batch_count, int b_shared, int relu) {
+    // Persistent CTA: tiles blockIdx.x, blockIdx.x + gridDim.x, ... ; two accumulator stages in TMEM
+    // so the epilogue of tile i overlaps the MMAs of tile i + 1.
     extern __shared__ unsigned char smem_raw[];
     constexpr uint32_t kBytesB = kBlockN * kGemmBlockK * 2;
-    constexpr uint32_t kTmemCols = kBlockN;
+    constexpr uint32_t kTmemCols = 2 * kBlockN;  // 128 / 256 / 512: a power of two
     using Smem = GemmSmem<kBlockN>;
     Smem& sm = *reinterpret_cast<Smem*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int m0 = blockIdx.x * kGemmBlockM, n0 = blockIdx.y * kBlockN, batch = blockIdx.z;
     const int num_kb = (k + kGemmBlockK - 1) / kGemmBlockK;
+    const int m_tiles = (m + kGemmBlockM - 1) / kGemmBlockM;
+    const int n_tiles = (n + kBlockN - 1) / kBlockN;
+    const long long num_tiles = (long long)m_tiles * n_tiles * batch_count;
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
@@ -136,7 +147,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
             mbar_init(&sm.full[s], 1);
             mbar_init(&sm.empty[s], 1);
         }
-        mbar_init(&sm.tmem_full, 1);
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(&sm.tmem_full[a], 1);
+            mbar_init(&sm.tmem_empty[a], 128);  // every epilogue thread arrives
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {  // whole warp: allocate the accumulator columns, then give the permit back
@@ -148,109 +162,135 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const uint32_t tmem_acc = sm.tmem_base;
+    const uint32_t tmem_base = sm.tmem_base;
 
     if (warp == 0) {
-        if (lane == 0) {  // ---- TMA producer
-            for (int kb = 0; kb < num_kb; ++kb) {
-                const int s = kb % kGemmStages;
-                const uint32_t phase = (kb / kGemmStages) & 1;
-                mbar_wait(&sm.empty[s], phase ^ 1);
-                mbar_expect_tx(&sm.full[s], kBytesA + kBytesB);
-                tma_load_3d(sm.a[s], &map_a, &sm.full[s], kb * kGemmBlockK, m0, batch);
-                tma_load_3d(sm.b[s], &map_b, &sm.full[s], kb * kGemmBlockK, n0, b_shared ? 0 : batch);
+        if (lane == 0) {  // ---- TMA producer: the ring runs straight through tile boundaries
+            uint32_t it = 0;
+            for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const int mt = (int)(tile % m_tiles), nt = (int)((tile / m_tiles) % n_tiles);
+                const int batch = (int)(tile / ((long long)m_tiles * n_tiles));
+                for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                    const int s = it % kGemmStages;
+                    const uint32_t phase = (it / kGemmStages) & 1;
+                    mbar_wait(&sm.empty[s], phase ^ 1);
+                    mbar_expect_tx(&sm.full[s], kBytesA + kBytesB);
+                    tma_load_3d(sm.a[s], &map_a, &sm.full[s], kb * kGemmBlockK, mt * kGemmBlockM, batch);
+                    tma_load_3d(sm.b[s], &map_b, &sm.full[s], kb * kGemmBlockK, nt * kBlockN, b_shared ? 0 : batch);
+                }
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {  // ---- MMA issuer
             const uint32_t idesc = umma_instr_desc<kBlockN>();
-            for (int kb = 0; kb < num_kb; ++kb) {
-                const int s = kb % kGemmStages;
-                const uint32_t phase = (kb / kGemmStages) & 1;
-                mbar_wait(&sm.full[s], phase);
+            uint32_t it = 0, local_tile = 0;
+            for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local_tile) {
+                const uint32_t acc = local_tile & 1, use = local_tile >> 1;
+                mbar_wait(&sm.tmem_empty[acc], (use & 1) ^ 1);  // epilogue has drained this stage
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t a_addr = smem_u32(sm.a[s]), b_addr = smem_u32(sm.b[s]);
+                const uint32_t tmem_acc = tmem_base + acc * kBlockN;
+                for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                    const int s = it % kGemmStages;
+                    const uint32_t phase = (it / kGemmStages) & 1;
+                    mbar_wait(&sm.full[s], phase);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t a_addr = smem_u32(sm.a[s]), b_addr = smem_u32(sm.b[s]);
 #pragma unroll
-                for (int kk = 0; kk < kGemmBlockK / kGemmUmmaK; ++kk) {
-                    // advancing 16 bf16 = 32 bytes along K stays inside the 128-byte swizzle row
-                    umma_bf16(tmem_acc, umma_smem_desc(a_addr + kk * kGemmUmmaK * 2),
-                              umma_smem_desc(b_addr + kk * kGemmUmmaK * 2), idesc, (kb | kk) != 0);
+                    for (int kk = 0; kk < kGemmBlockK / kGemmUmmaK; ++kk) {
+                        // advancing 16 bf16 = 32 bytes along K stays inside the 128-byte swizzle row
+                        umma_bf16(tmem_acc, umma_smem_desc(a_addr + kk * kGemmUmmaK * 2),
+                                  umma_smem_desc(b_addr + kk * kGemmUmmaK * 2), idesc, (kb | kk) != 0);
+                    }
+                    umma_commit(&sm.empty[s]);  // frees the ring slot when these MMAs have read it
                 }
-                umma_commit(&sm.empty[s]);  // frees the ring slot when these MMAs have read it
+                umma_commit(&sm.tmem_full[acc]);  // accumulator stage complete
             }
-            umma_commit(&sm.tmem_full);     // accumulator complete
         }
     } else {
         // ---- epilogue: warp w may touch TMEM lanes [32 * (w % 4), +32)
         const int quarter = warp & 3;
-        const int row = m0 + quarter * 32 + lane;
-        mbar_wait(&sm.tmem_full, 0);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const float* bias_b = bias != nullptr ? bias + (long long)batch * bias_batch_stride : nullptr;
+        uint32_t local_tile = 0;
+        for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local_tile) {
+            const int mt = (int)(tile % m_tiles), nt = (int)((tile / m_tiles) % n_tiles);
+            const int batch = (int)(tile / ((long long)m_tiles * n_tiles));
+            const int m0 = mt * kGemmBlockM, n0 = nt * kBlockN;
+            const uint32_t acc = local_tile & 1, use = local_tile >> 1;
+            const int row = m0 + quarter * 32 + lane;
+            mbar_wait(&sm.tmem_full[acc], use & 1);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t tmem_acc = tmem_base + acc * kBlockN;
+            const float* bias_b = bias != nullptr ? bias + (long long)batch * bias_batch_stride : nullptr;
+#pragma unroll 1
+            for (int chunk = 0; chunk < kBlockN / 32; ++chunk) {
+                if (n0 + chunk * 32 >= n) break;  // columns past N hold zeros: nothing to store
+                uint32_t r[32];
+                const uint32_t taddr = tmem_acc + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(chunk * 32);
+                asm volatile(
+                    "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                    "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                    "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                    : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                      "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]),
+                      "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]),
+                      "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]),
+                      "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+                    : "r"(taddr)
+                    : "memory");
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (row < m) {
+                    const int col0 = n0 + chunk * 32;
+                    const long long out_off = ((long long)batch * m + row) * n + col0;
+                    float v[32];
 #pragma unroll
-        for (int chunk = 0; chunk < kBlockN / 32; ++chunk) {
-            uint32_t r[32];
-            const uint32_t taddr = tmem_acc + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(chunk * 32);
-            asm volatile(
-                "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-                "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-                "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-                  "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]),
-                  "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]),
-                  "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]),
-                  "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-                : "r"(taddr)
-                : "memory");
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-            if (row < m) {
-                const int col0 = n0 + chunk * 32;
-                const long long out_off = ((long long)batch * m + row) * n + col0;
-                float v[32];
+                    for (int j = 0; j < 32; ++j) {
+                        v[j] = __uint_as_float(r[j]);
+                        if (bias_b != nullptr && col0 + j < n) v[j] += bias_b[col0 + j];
+                        if (relu) v[j] = fmaxf(v[j], 0.f);
+                    }
+                    const bool full = col0 + 32 <= n;
+                    if (out_bf16) {
+                        __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(c) + out_off;
+                        if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+                            // 32 columns = 64 bytes: four 128-bit stores of packed bf16 pairs
 #pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    v[j] = __uint_as_float(r[j]);
-                    if (bias_b != nullptr && col0 + j < n) v[j] += bias_b[col0 + j];
-                    if (relu) v[j] = fmaxf(v[j], 0.f);
-                }
-                const bool full = col0 + 32 <= n;
-                if (out_bf16) {
-                    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(c) + out_off;
-                    if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
-                        // 32 columns = 64 bytes: four 128-bit stores of packed bf16 pairs
+                            for (int q = 0; q < 4; ++q) {
+                                uint4 pk;
+                                __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&pk);
 #pragma unroll
-                        for (int q = 0; q < 4; ++q) {
-                            uint4 pk;
-                            __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&pk);
+                                for (int e = 0; e < 4; ++e)
+                                    h[e] = __floats2bfloat162_rn(v[8 * q + 2 * e], v[8 * q + 2 * e + 1]);
+                                reinterpret_cast<uint4*>(dst)[q] = pk;
+                            }
+                        } else {
 #pragma unroll
-                            for (int e = 0; e < 4; ++e) h[e] = __floats2bfloat162_rn(v[8 * q + 2 * e], v[8 * q + 2 * e + 1]);
-                            reinterpret_cast<uint4*>(dst)[q] = pk;
+                            for (int j = 0; j < 32; ++j)
+                                if (col0 + j < n) dst[j] = __float2bfloat16(v[j]);
                         }
                     } else {
+                        float* dst = reinterpret_cast<float*>(c) + out_off;
+                        if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            if (col0 + j < n) dst[j] = __float2bfloat16(v[j]);
-                    }
-                } else {
-                    float* dst = reinterpret_cast<float*>(c) + out_off;
-                    if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+                            for (int q = 0; q < 8; ++q)
+                                reinterpret_cast<float4*>(dst)[q] =
+                                    make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+                        } else {
 #pragma unroll
-                        for (int q = 0; q < 8; ++q)
-                            reinterpret_cast<float4*>(dst)[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            if (col0 + j < n) dst[j] = v[j];
+                            for (int j = 0; j < 32; ++j)
+                                if (col0 + j < n) dst[j] = v[j];
+                        }
                     }
                 }
             }
+            // this thread's TMEM reads of the stage are complete: hand the stage back to the MMA warp
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            mbar_arrive(&sm.tmem_empty[acc]);
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (warp == 1) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_acc), "r"(kTmemCols) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
     }
 }
 
@@ -298,7 +338,6 @@ extern "C" int dls_gemm_bf16_tn(const void* a, const void* b, const float* bias,
     if (k % 8) return fail_msg("dls_gemm_bf16_tn: K must be a multiple of 8 (16-byte rows for TMA)");
     if (((uintptr_t)a | (uintptr_t)b) & 15) return fail_msg("dls_gemm_bf16_tn: operands must be 16-byte aligned");
     if (out_dtype != 0 && out_dtype != 1) return fail_msg("dls_gemm_bf16_tn: out_dtype must be 0 (fp32) or 1 (bf16)");
-    if (batch > 65535) return fail_msg("dls_gemm_bf16_tn: batch too large");
     CUtensorMap map_a, map_b;
     if (int rc = make_map(&map_a, a, m, k, batch, kGemmBlockM)) return rc;
     // tile width: narrow outputs keep a narrow tile; wide ones take 256 columns when that still
@@ -310,7 +349,8 @@ extern "C" int dls_gemm_bf16_tn(const void* a, const void* b, const float* bias,
     static const int forced = [] { const char* e = getenv("DLS_GEMM_BN"); return e ? atoi(e) : 0; }();  // tuning knob
     if ((forced == 64 || forced == 128 || forced == 256) && n > forced / 2) block_n = forced;
     if (int rc = make_map(&map_b, b, n, k, b_shared ? 1 : batch, block_n)) return rc;
-    dim3 grid((unsigned)m_tiles, (n + block_n - 1) / block_n, batch);
+    const long long num_tiles = m_tiles * ((n + block_n - 1) / block_n) * batch;
+    dim3 grid((unsigned)(num_tiles < kNumSMs ? num_tiles : kNumSMs));  // persistent: one CTA per SM
     const long long bias_stride = b_shared ? 0 : (long long)n;
     cudaStream_t s = (cudaStream_t)stream;
 #define DLS_GEMM_LAUNCH(BN)                                                                                   \
@@ -323,7 +363,7 @@ extern "C" int dls_gemm_bf16_tn(const void* a, const void* b, const float* bias,
             configured = true;                                                                                \
         }                                                                                                     \
         gemm_bf16_tcgen05_kernel<BN><<<grid, kGemmThreads, smem, s>>>(map_a, map_b, bias, bias_stride, c, out_dtype, \
-                                                                      m, n, k, b_shared, relu);               \
+                                                                      m, n, k, batch, b_shared, relu);        \
     } while (0)
     if (block_n == 256) DLS_GEMM_LAUNCH(256);
     else if (block_n == 128) DLS_GEMM_LAUNCH(128);
