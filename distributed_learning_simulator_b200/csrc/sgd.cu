@@ -9,6 +9,8 @@
 // addresses are fixed but not contiguous) and the step's learning rate from a device-side
 // schedule table indexed by a device-side step counter -- nothing in the captured graph
 // depends on a host value, so one graph serves every step of every round.
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 #include "../../include/dls_b200.h"
 
@@ -20,7 +22,7 @@ __global__ void __launch_bounds__(kSgdThreads)
 sgd_step_kernel(float* __restrict__ params, float* __restrict__ mom, const float* const* __restrict__ grads,
                 const long long* __restrict__ tensor_offsets, int n_tensors, const float* __restrict__ lr_table,
                 int lr_len, const int32_t* __restrict__ state, float weight_decay, float momentum, float dampening,
-                int nesterov) {
+                int nesterov, const uint8_t* __restrict__ grad_is_bf16, __nv_bfloat16* __restrict__ shadow) {
     extern __shared__ long long s_off[];
     for (int i = threadIdx.x; i <= n_tensors; i += blockDim.x) s_off[i] = tensor_offsets[i];
     __syncthreads();
@@ -37,10 +39,18 @@ sgd_step_kernel(float* __restrict__ params, float* __restrict__ mom, const float
         const long long j = i - s_off[t];
         const bool fast = (i + 4 <= s_off[t + 1]) && ((j & 3) == 0) && grads[t] != nullptr;
         float g[4], p[4], m[4];
+        const bool half_grad = grad_is_bf16 != nullptr && grad_is_bf16[t] != 0;
         if (fast) {
-            const float4 gv = ld_stream_f4(grads[t] + j);  // gradients are read exactly once
+            if (half_grad) {  // mixed precision: the model's matrix is the bf16 shadow, so is its gradient
+                const uint2 raw = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(grads[t]) + j);
+                const float2 lo = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.x));
+                const float2 hi = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.y));
+                g[0] = lo.x; g[1] = lo.y; g[2] = hi.x; g[3] = hi.y;
+            } else {
+                const float4 gv = ld_stream_f4(grads[t] + j);  // gradients are read exactly once
+                g[0] = gv.x; g[1] = gv.y; g[2] = gv.z; g[3] = gv.w;
+            }
             const float4 pv = *reinterpret_cast<const float4*>(params + i);
-            g[0] = gv.x; g[1] = gv.y; g[2] = gv.z; g[3] = gv.w;
             p[0] = pv.x; p[1] = pv.y; p[2] = pv.z; p[3] = pv.w;
             if (momentum != 0.f) {
                 const float4 mv = *reinterpret_cast<const float4*>(mom + i);
@@ -57,6 +67,12 @@ sgd_step_kernel(float* __restrict__ params, float* __restrict__ mom, const float
             }
             *reinterpret_cast<float4*>(params + i) = make_float4(p[0], p[1], p[2], p[3]);
             if (momentum != 0.f) *reinterpret_cast<float4*>(mom + i) = make_float4(m[0], m[1], m[2], m[3]);
+            if (half_grad && shadow != nullptr) {  // refresh the bf16 compute copy in the same pass
+                uint2 out;
+                *reinterpret_cast<__nv_bfloat162*>(&out.x) = __floats2bfloat162_rn(p[0], p[1]);
+                *reinterpret_cast<__nv_bfloat162*>(&out.y) = __floats2bfloat162_rn(p[2], p[3]);
+                *reinterpret_cast<uint2*>(shadow + i) = out;
+            }
         } else {
             for (int e = 0; e < 4; ++e) {
                 const long long ie = i + e;
@@ -64,13 +80,17 @@ sgd_step_kernel(float* __restrict__ params, float* __restrict__ mom, const float
                 const int te = find_segment(s_off, n_tensors, ie);
                 const float* gp = grads[te];
                 if (gp == nullptr) continue;  // parameter received no gradient this step
-                float d = gp[ie - s_off[te]] + weight_decay * params[ie];
+                const bool half_e = grad_is_bf16 != nullptr && grad_is_bf16[te] != 0;
+                const float ge = half_e ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(gp)[ie - s_off[te]])
+                                        : gp[ie - s_off[te]];
+                float d = ge + weight_decay * params[ie];
                 if (momentum != 0.f) {
                     const float mm = mom_ready ? momentum * mom[ie] + (1.f - dampening) * d : d;
                     mom[ie] = mm;
                     d = nesterov ? d + momentum * mm : mm;
                 }
                 params[ie] -= lr * d;
+                if (half_e && shadow != nullptr) shadow[ie] = __float2bfloat16(params[ie]);
             }
         }
     }
@@ -158,7 +178,7 @@ using namespace dls;
 extern "C" int dls_sgd_step(float* params, float* momentum_buf, const float* const* grads,
                             const long long* tensor_offsets, int n_tensors, const float* lr_table, int lr_len,
                             const int32_t* state, float weight_decay, float momentum, float dampening, int nesterov,
-                            void* stream) {
+                            const uint8_t* grad_is_bf16, void* shadow_bf16, void* stream) {
     if (n_tensors < 1 || n_tensors > 5000) return fail_msg("dls_sgd_step: n_tensors must be in [1, 5000]");
     if (lr_len < 1) return fail_msg("dls_sgd_step: empty lr table");
     if (momentum != 0.f && momentum_buf == nullptr) return fail_msg("dls_sgd_step: momentum buffer missing");
@@ -167,7 +187,9 @@ extern "C" int dls_sgd_step(float* params, float* momentum_buf, const float* con
     const int grid = kNumSMs * 8;
     sgd_step_kernel<<<grid, kSgdThreads, smem, (cudaStream_t)stream>>>(params, momentum_buf, grads, tensor_offsets,
                                                                          n_tensors, lr_table, lr_len, state,
-                                                                         weight_decay, momentum, dampening, nesterov);
+                                                                         weight_decay, momentum, dampening, nesterov,
+                                                                         grad_is_bf16,
+                                                                         reinterpret_cast<__nv_bfloat16*>(shadow_bf16));
     DLS_LAUNCHED("sgd_step_kernel");
     return 0;
 }

@@ -50,3 +50,69 @@ def get_device(max_needed_bytes: int | None = None, index: int | None = None) ->
         if free < max_needed_bytes:
             raise RuntimeError(f"{device} has {free} free bytes, {max_needed_bytes} needed")
     return device
+
+
+class CaptureGuard:
+    """Keeps library-backed eager work (cuDNN/cuBLAS forward passes of evaluations and eager
+    training loops, which may autotune, allocate or synchronise) away from a CUDA-graph capture
+    running in another role thread of the same process.  Eager sections hold the guard shared
+    (re-entrant per thread); a capture holds it exclusively and has priority over new sharers.
+    Graph replays and this framework's own kernels never take it."""
+
+    def __init__(self) -> None:
+        self._cond = threading.Condition()
+        self._sharers = 0
+        self._capturing = False
+        self._waiting_captures = 0
+        self._local = threading.local()
+
+    class _Shared:
+        def __init__(self, guard: "CaptureGuard") -> None:
+            self.guard = guard
+
+        def __enter__(self) -> None:
+            g = self.guard
+            depth = getattr(g._local, "depth", 0)
+            if depth == 0:
+                with g._cond:
+                    while g._capturing or g._waiting_captures:
+                        g._cond.wait()
+                    g._sharers += 1
+            g._local.depth = depth + 1
+
+        def __exit__(self, *exc: object) -> None:
+            g = self.guard
+            g._local.depth -= 1
+            if g._local.depth == 0:
+                with g._cond:
+                    g._sharers -= 1
+                    g._cond.notify_all()
+
+    class _Exclusive:
+        def __init__(self, guard: "CaptureGuard") -> None:
+            self.guard = guard
+
+        def __enter__(self) -> None:
+            g = self.guard
+            assert getattr(g._local, "depth", 0) == 0, "capture requested inside an eager section"
+            with g._cond:
+                g._waiting_captures += 1
+                while g._capturing or g._sharers:
+                    g._cond.wait()
+                g._waiting_captures -= 1
+                g._capturing = True
+
+        def __exit__(self, *exc: object) -> None:
+            g = self.guard
+            with g._cond:
+                g._capturing = False
+                g._cond.notify_all()
+
+    def shared(self) -> "CaptureGuard._Shared":
+        return CaptureGuard._Shared(self)
+
+    def exclusive(self) -> "CaptureGuard._Exclusive":
+        return CaptureGuard._Exclusive(self)
+
+
+capture_guard = CaptureGuard()

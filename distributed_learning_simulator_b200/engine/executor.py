@@ -10,6 +10,7 @@ from torch import nn
 
 from .dataloader import Batch, create_loader
 from .dataset import DatasetCollection
+from .device import capture_guard
 from .hook import HookCollection
 from .hyper_parameter import HyperParameter
 from .log import get_logger
@@ -173,7 +174,9 @@ class ModelExecutor(HookCollection):
         metric = PerformanceMetric()
         was_training = self._model.training
         self._model.eval()
-        with torch.no_grad(), self._stream_context():
+        with self._stream_context():
+            self._model_util.refresh_shadow()  # the fp32 arena may have been written in place since
+        with capture_guard.shared(), torch.no_grad(), self._stream_context():
             metric.start_epoch(self._device)
             if self._dc.get_dataset_size(phase) > 0:
                 for batch in self._loader(phase):

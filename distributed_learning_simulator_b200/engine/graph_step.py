@@ -14,7 +14,6 @@ The reference's counterpart is the external ``Trainer.train()`` eager loop with
 /root/reference/simulation_lib/worker/worker.py:86-88.
 """
 import os
-import threading
 import time
 from typing import Any
 
@@ -23,12 +22,14 @@ import torch
 from ..ops import runtime
 from ..ops import sgd as sgd_ops
 from .dataloader import SampleLoader
+from .device import capture_guard
 from .log import get_logger
 from .ml_type import ExecutorHookPoint, MachineLearningPhase
 
 
-# captures are serialised; other threads keep running eager work (thread-local capture mode)
-_capture_lock = threading.Lock()
+# captures are serialised and exclude other threads' cuDNN/cuBLAS eager sections (device.CaptureGuard);
+# graph replays and this framework's own kernels keep running (thread-local capture mode)
+_capture_lock = capture_guard.exclusive
 
 # process-wide counters read by bench.py
 REPLAY_COUNTER = [0]
@@ -65,6 +66,13 @@ class GraphTrainStep:
         self.n_tensors = len(self.layout.names)
         self.offsets = torch.tensor(self.layout.offsets, dtype=torch.int64, device=self.device)
         self.momentum_buf = torch.zeros_like(self.flat)
+        # mixed precision: matrices/filters of the model are bf16 views of a shadow arena that the
+        # fused SGD kernel rewrites, so no weight or gradient cast kernel runs inside the step
+        self.use_shadow = bool(trainer.hook_config.use_amp) and os.environ.get("DLS_BF16_SHADOW", "1") != "0"
+        self.shadow: torch.Tensor | None = None
+        self.shadow_flags: torch.Tensor | None = None
+        if self.use_shadow:
+            self.shadow_flags = torch.tensor(self.util.shadow_flags(), dtype=torch.uint8, device=self.device)
         # state: [0] lr/optimizer step, [1] momentum initialised, [2] batch index in epoch
         self.state = torch.zeros(4, dtype=torch.int32, device=self.device)
         self.acc = torch.zeros(3, dtype=torch.float64, device=self.device)
@@ -103,7 +111,8 @@ class GraphTrainStep:
         if step.grad_table is None:
             step.grad_table = torch.zeros(self.n_tensors, dtype=torch.int64, device=self.device)
         sgd_ops.sgd_step(self.flat, self.momentum_buf if hp.momentum else None, step.grad_table, self.offsets,
-                         self.n_tensors, self.lr_table, self.state, hp.weight_decay, hp.momentum)
+                         self.n_tensors, self.lr_table, self.state, hp.weight_decay, hp.momentum,
+                         grad_is_bf16=self.shadow_flags, shadow=self.shadow)
         sgd_ops.sgd_tick(self.state)
         sgd_ops.metric_accumulate(output.float().contiguous(), step.y, loss.detach().reshape(1), self.acc)
 
@@ -114,11 +123,11 @@ class GraphTrainStep:
         for p, g in zip(params, step.grads):
             # the fused update walks physical memory: a gradient must be laid out like its parameter
             # (autograd's layout contract gives channels-last grads for channels-last weights)
-            assert g is None or (g.dtype == torch.float32 and _same_physical_layout(g, p)), (g.stride(), p.stride())
+            assert g is None or (g.dtype == p.dtype and _same_physical_layout(g, p)), (g.stride(), p.stride())
         step.grad_table.copy_(torch.tensor(ptrs, dtype=torch.int64))
 
     def _capture(self, batch: int, x_all: torch.Tensor, y_all: torch.Tensor, n_order: int) -> _CapturedStep:
-        with _capture_lock:
+        with _capture_lock():
             before = runtime.launch_count()
             step = self._capture_locked(batch, x_all, y_all, n_order)
             CAPTURE_LAUNCHES[0] += runtime.launch_count() - before
@@ -154,6 +163,7 @@ class GraphTrainStep:
         step.own_kernels = runtime.launch_count() - own_before  # own kernel nodes in one replay
         self._fill_grad_table(step)
         self.flat.copy_(saved[0])
+        self.util.refresh_shadow()
         self.momentum_buf.copy_(saved[1])
         self.state.copy_(saved[2])
         self.acc.copy_(saved[3])
@@ -170,6 +180,12 @@ class GraphTrainStep:
         self.active = True
         batch = hp.batch_size
         with torch.cuda.stream(t.stream):
+            if self.use_shadow:
+                shadow = self.util.enable_shadow()
+                if self.shadow is None or shadow.data_ptr() != self.shadow.data_ptr():
+                    self.steps.clear()  # captured kernels hold the shadow's address
+                self.shadow = shadow
+                self.util.refresh_shadow()  # aggregation may have written the fp32 arena in place
             x_all, y_all, order0 = loader.epoch_tensors()  # shuffled order for epoch 1
             n = order0.numel()
             full, rem = divmod(n, batch)

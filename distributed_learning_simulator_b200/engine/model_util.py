@@ -119,6 +119,8 @@ class ModelUtil:
         self.__flat: torch.Tensor | None = None
         self.__flat_grad: torch.Tensor | None = None
         self.__layout: ParameterLayout | None = None
+        self.__shadow: torch.Tensor | None = None  # bf16 compute copy of the arena (see enable_shadow)
+        self.__shadow_store: torch.Tensor | None = None  # kept across disable/enable: CUDA graphs hold its address
 
     @property
     def model(self) -> nn.Module:
@@ -126,6 +128,9 @@ class ModelUtil:
 
     # ---- parameters -----------------------------------------------------------
     def get_parameter_dict(self, detach: bool = True) -> TensorDict:
+        if self.__shadow is not None:
+            # the model's matrices are bf16 compute copies: the parameters ARE the fp32 master arena
+            return self.layout.views(self.__flat)
         res = {}
         for name, p in self.__model.named_parameters():
             res[name] = p.detach() if detach else p
@@ -143,17 +148,19 @@ class ModelUtil:
         return self.__layout
 
     def load_parameter_dict(self, parameter_dict: TensorDict, check_parameter: bool = False) -> None:
-        own = dict(self.__model.named_parameters())
+        own = self.get_parameter_dict() if self.__shadow is not None else dict(self.__model.named_parameters())
         if check_parameter:
             assert set(own) == set(parameter_dict), "parameter names differ"
         with torch.no_grad():
             for name, value in parameter_dict.items():
                 own[name].copy_(value.to(own[name].device, non_blocking=True))
+        self.refresh_shadow()
 
     def load_parameter_list(self, flat: torch.Tensor) -> None:
         with torch.no_grad():
             if self.__flat is not None:
                 self.__flat.copy_(flat.to(self.__flat.device, non_blocking=True))
+                self.refresh_shadow()
                 return
             off = 0
             for p in self.__model.parameters():
@@ -192,13 +199,70 @@ class ModelUtil:
                 off += n
         self.__flat, self.__flat_grad = flat, flat_grad
         self.__layout = None
+        self.__shadow_store = None
         return flat
 
     def is_flat(self) -> bool:
         if self.__flat is None:
             return False
         base = self.__flat.untyped_storage().data_ptr()
+        if self.__shadow is not None:
+            sbase = self.__shadow.untyped_storage().data_ptr()
+            return all(p.data.untyped_storage().data_ptr() in (base, sbase) for p in self.__model.parameters())
         return all(p.data.untyped_storage().data_ptr() == base for p in self.__model.parameters())
+
+    # ---- bf16 compute shadow ---------------------------------------------------------
+    @property
+    def shadow(self) -> torch.Tensor | None:
+        return self.__shadow
+
+    def shadow_flags(self) -> list[int]:
+        """1 for tensors whose model parameter is the bf16 shadow copy: matrices / filters whose
+        shadow segment starts on a 16-byte boundary (cuDNN/cuBLAS pick their vectorised kernels by
+        pointer alignment; an arena offset that is fine for fp32 can be misaligned at 2 bytes/element)."""
+        layout = self.layout
+        return [int(len(shape) >= 2 and off % 8 == 0) for shape, off in zip(layout.shapes, layout.offsets)]
+
+    def enable_shadow(self) -> torch.Tensor:
+        """Mixed-precision training without per-step cast kernels: every >= 2-D parameter of the
+        model becomes a bf16 view into a second ("shadow") arena with the same segment layout, while
+        the fp32 arena stays the master copy that is exchanged, check-pointed and updated by the
+        fused SGD kernel (which rewrites the shadow in the same pass).  1-D parameters (BatchNorm
+        scale/shift, biases) stay fp32 views of the master."""
+        assert self.__flat is not None and self.is_flat()
+        if self.__shadow is not None:
+            return self.__shadow
+        layout = self.layout
+        shadow = self.__shadow_store
+        if shadow is None or shadow.device != self.__flat.device or shadow.numel() != layout.total:
+            shadow = torch.empty(layout.total, dtype=torch.bfloat16, device=self.__flat.device)
+        self.__shadow_store = shadow
+        shadow.copy_(self.__flat)
+        params = dict(self.__model.named_parameters())
+        flags = self.shadow_flags()
+        for i, name in enumerate(layout.names):
+            if flags[i]:
+                p = params[name]
+                p.data = layout.view_of(shadow, i)
+                p.grad = None
+        self.__shadow = shadow
+        return shadow
+
+    def disable_shadow(self) -> None:
+        if self.__shadow is None:
+            return
+        layout = self.layout
+        params = dict(self.__model.named_parameters())
+        self.__shadow = None
+        for i, name in enumerate(layout.names):
+            p = params[name]
+            p.data = layout.view_of(self.__flat, i)
+            p.grad = None
+
+    def refresh_shadow(self) -> None:
+        if self.__shadow is not None:
+            with torch.no_grad():
+                self.__shadow.copy_(self.__flat)
 
     @property
     def flat_parameter(self) -> torch.Tensor | None:
@@ -223,6 +287,7 @@ class ModelUtil:
         first = next(self.__model.parameters(), None)
         if first is not None and first.device == device:
             return
+        self.disable_shadow()
         self.__model.to(device)
         self.__flat = None
         self.__flat_grad = None

@@ -13,17 +13,23 @@ util/model.py:6-23).  Two execution paths share the same hooks:
   captured once in a CUDA graph and replayed per batch on the worker's own stream.
 """
 import time
+import warnings
 from typing import Any
 
 import torch
 from torch import nn
 
 from .dataset import DatasetCollection
+from .device import capture_guard
 from .executor import HookConfig, ModelExecutor
 from .hyper_parameter import HyperParameter
 from .log import get_logger
 from .ml_type import ExecutorHookPoint, MachineLearningPhase, StopExecutingException
 from .tensor import TensorDict
+
+# a hook may own the optimizer step (sign_SGD applies the server's majority vote), so the scheduler
+# can legitimately tick without torch having seen optimizer.step()
+warnings.filterwarnings("ignore", message=r"Detected call of `lr_scheduler\.step\(\)` before")
 
 
 class Trainer(ModelExecutor):
@@ -94,7 +100,8 @@ class Trainer(ModelExecutor):
             with self._stream_context():
                 self.exec_hooks(ExecutorHookPoint.BEFORE_EXECUTE, executor=self)
                 if self._needs_eager():
-                    self._train_eager()
+                    with capture_guard.shared():
+                        self._train_eager()
                 else:
                     self._train_graph()
                 self.exec_hooks(ExecutorHookPoint.AFTER_EXECUTE, executor=self, epoch=self._hyper_parameter.epoch)
@@ -125,6 +132,7 @@ class Trainer(ModelExecutor):
         return self._hyper_parameter.learning_rate
 
     def _train_eager(self) -> None:
+        self._model_util.disable_shadow()  # torch.optim updates fp32 parameters
         optimizer = self.get_optimizer()
         loader = self._loader(MachineLearningPhase.Training)
         scheduler = self._get_lr_scheduler(self._hyper_parameter.epoch * len(loader))

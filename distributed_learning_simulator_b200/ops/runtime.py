@@ -31,7 +31,7 @@ _SIGNATURES = {
     "dls_fedavg_reduce_packed": [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p,
                                  c_void_p],
     "dls_sgd_step": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_float, c_float,
-                     c_float, c_int, c_void_p],
+                     c_float, c_int, c_void_p, c_void_p, c_void_p],
     "dls_sgd_tick": [c_void_p, c_void_p],
     "dls_gather_batch": [c_void_p, c_void_p, c_void_p, c_ll, c_void_p, c_int, c_int, c_int, c_ll, c_int,
                          c_void_p, c_void_p, c_void_p],

@@ -8,11 +8,14 @@ from . import runtime
 
 def sgd_step(params: torch.Tensor, momentum_buf: torch.Tensor | None, grad_table: torch.Tensor,
              tensor_offsets: torch.Tensor, n_tensors: int, lr_table: torch.Tensor, state: torch.Tensor,
-             weight_decay: float, momentum: float, dampening: float = 0.0, nesterov: bool = False) -> None:
+             weight_decay: float, momentum: float, dampening: float = 0.0, nesterov: bool = False,
+             grad_is_bf16: torch.Tensor | None = None, shadow: torch.Tensor | None = None) -> None:
+    """``grad_is_bf16`` (uint8 [n_tensors]) + ``shadow`` (bf16 arena): mixed-precision mode, see
+    ``ModelUtil.enable_shadow``."""
     runtime.call("dls_sgd_step", params.data_ptr(), runtime.ptr(momentum_buf), grad_table.data_ptr(),
                  tensor_offsets.data_ptr(), n_tensors, lr_table.data_ptr(), lr_table.numel(), state.data_ptr(),
                  float(weight_decay), float(momentum), float(dampening), int(nesterov),
-                 runtime.stream_ptr(params.device))
+                 runtime.ptr(grad_is_bf16), runtime.ptr(shadow), runtime.stream_ptr(params.device))
 
 
 def sgd_tick(state: torch.Tensor) -> None:

@@ -67,10 +67,14 @@ int dls_copy_device(void* dst, const void* src, long long bytes, void* stream); 
  * Multi-tensor fused SGD over the flat parameter arena: gradients are read through a
  * device pointer table (one entry per tensor), weight decay, momentum/dampening/
  * nesterov, lr = lr_table[min(state[0], lr_len-1)].  state[1] == 0 means "momentum
- * buffer not initialised" (first step copies the gradient like torch.optim.SGD). */
+ * buffer not initialised" (first step copies the gradient like torch.optim.SGD).
+ * Mixed precision: grad_is_bf16[t] != 0 (device [n_tensors], may be NULL) marks tensors whose
+ * gradient is bf16; for those the updated fp32 value is also written, rounded, to the bf16
+ * shadow arena `shadow_bf16` (same offsets; may be NULL) so no cast kernel runs per step. */
 int dls_sgd_step(float* params, float* momentum_buf, const float* const* grads, const long long* tensor_offsets,
                  int n_tensors, const float* lr_table, int lr_len, const int32_t* state, float weight_decay,
-                 float momentum, float dampening, int nesterov, void* stream);
+                 float momentum, float dampening, int nesterov, const uint8_t* grad_is_bf16, void* shadow_bf16,
+                 void* stream);
 /* state[0] += 1 (schedule step); state[1] = 1 (momentum ready); state[2] += 1 (batch index in epoch) */
 int dls_sgd_tick(int32_t* state, void* stream);
 /* x_out[b,:] = x_all[order[state[state_index]*batch_stride + b], :] for b < batch, y likewise;

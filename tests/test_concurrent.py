@@ -55,3 +55,48 @@ def test_random_label_iid_sampler():
     assert seen == set(range(10))
     total = sum(len(v) for v in sampler._dataset_indices[MachineLearningPhase.Training].values())
     assert total == 2000
+
+
+def test_capture_guard_excludes_eager_sections():
+    """device.CaptureGuard: shared sections overlap each other, are re-entrant, and never overlap an
+    exclusive (capture) section; a waiting capture is not starved by new sharers."""
+    import threading
+    import time
+
+    from distributed_learning_simulator_b200.engine.device import CaptureGuard
+
+    guard = CaptureGuard()
+    state = {"shared": 0, "max_shared": 0, "exclusive": 0, "violations": 0}
+    lock = threading.Lock()
+
+    def eager(n: int) -> None:
+        for _ in range(n):
+            with guard.shared():
+                with guard.shared():  # nested evaluate inside an eager epoch
+                    with lock:
+                        state["shared"] += 1
+                        state["max_shared"] = max(state["max_shared"], state["shared"])
+                        state["violations"] += state["exclusive"]
+                    time.sleep(0.002)
+                    with lock:
+                        state["shared"] -= 1
+
+    def capture(n: int) -> None:
+        for _ in range(n):
+            with guard.exclusive():
+                with lock:
+                    state["exclusive"] += 1
+                    state["violations"] += state["shared"] + (state["exclusive"] - 1)
+                time.sleep(0.003)
+                with lock:
+                    state["exclusive"] -= 1
+            time.sleep(0.001)
+
+    threads = [threading.Thread(target=eager, args=(40,)) for _ in range(4)]
+    threads += [threading.Thread(target=capture, args=(10,)) for _ in range(2)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(timeout=60)
+    assert not any(t.is_alive() for t in threads)
+    assert state["violations"] == 0 and state["max_shared"] >= 2

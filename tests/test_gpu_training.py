@@ -36,6 +36,30 @@ def test_graph_step_matches_eager():
         assert abs(out["metrics"]["g1"][e]["accuracy"] - out["metrics"]["e1"][e]["accuracy"]) < 1e-6
 
 
+def test_amp_graph_step_with_bf16_shadow_matches_autocast_eager():
+    """use_amp: the captured step trains matrices/filters as bf16 views of the shadow arena (no cast
+    kernels, the fused SGD kernel consumes bf16 gradients and rewrites the shadow); the eager arm is
+    stock autocast + torch.optim.SGD.  The arithmetic is the same - bf16(master) weights, bf16
+    gradients widened exactly - so with the same data order and init the fp32 masters agree."""
+    import json
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    arms = [({}, 2 * 22), ({"DATASET": "CIFAR10", "MODEL": "resnet18", "TRAIN": "300", "EPOCHS": "1"}, 10)]
+    for extra, replays in arms:
+        env = dict(os.environ, AMP="1", ORDER="g1,e1", **extra)
+        res = subprocess.run([sys.executable, os.path.join(root, "tools", "check_graph_step.py")],
+                             capture_output=True, text=True, timeout=600, env=env)
+        assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
+        out = json.loads(res.stdout.strip().splitlines()[-1])
+        assert out["replays"]["g1"] == replays and out["shadowed"]["g1"] >= 2 and out["shadowed"]["e1"] == 0
+        assert out["diffs"]["g1-e1"] < 1e-5, out["diffs"]
+        for g, e in zip(out["metrics"]["g1"], out["metrics"]["e1"]):
+            assert abs(g["loss"] - e["loss"]) < 1e-5 and abs(g["accuracy"] - e["accuracy"]) < 1e-6
+
+
 def test_fed_avg_on_gpu_uses_fused_paths():
     from distributed_learning_simulator_b200 import load_config_from_dict, train
     from distributed_learning_simulator_b200.ops import runtime

@@ -197,6 +197,46 @@ def test_sgd_step_matches_torch(dev, momentum, nesterov, wd):
     assert state.tolist()[:3] == [3, 1, 3]
 
 
+def test_sgd_step_bf16_gradients_and_shadow(dev):
+    """Mixed precision: flagged tensors hand the kernel a bf16 gradient and get their updated value
+    written to the bf16 shadow arena; the fp32 master follows torch.optim.SGD on the widened gradient."""
+    from distributed_learning_simulator_b200.ops import sgd as S
+
+    layout = _layout(NUMELS)
+    flags_host = [int(n >= 1000 or n == 33) for n in NUMELS]  # includes an odd-sized, unaligned segment
+    params = [torch.nn.Parameter(torch.randn(n, device=dev)) for n in NUMELS]
+    ref_opt = torch.optim.SGD(params, lr=0.1, momentum=0.9, weight_decay=1e-4)
+    flat = torch.cat([p.detach() for p in params]).clone()
+    shadow = flat.to(torch.bfloat16)
+    untouched = shadow.clone()
+    mom = torch.zeros_like(flat)
+    offsets = torch.tensor(layout.offsets, dtype=torch.int64, device=dev)
+    flags = torch.tensor(flags_host, dtype=torch.uint8, device=dev)
+    lr_table = torch.tensor([0.1, 0.05], device=dev)
+    state = torch.zeros(4, dtype=torch.int32, device=dev)
+    for step in range(2):
+        grads = [torch.randn(n, device=dev).to(torch.bfloat16 if f else torch.float32)
+                 for n, f in zip(NUMELS, flags_host)]
+        for p, g in zip(params, grads):
+            p.grad = g.float()
+        for group in ref_opt.param_groups:
+            group["lr"] = float(lr_table[step])
+        ref_opt.step()
+        table = torch.tensor([g.data_ptr() for g in grads], dtype=torch.int64, device=dev)
+        S.sgd_step(flat, mom, table, offsets, len(NUMELS), lr_table, state, 1e-4, 0.9, 0.0, False,
+                   grad_is_bf16=flags, shadow=shadow)
+        S.sgd_tick(state)
+        torch.cuda.synchronize()
+        ref = torch.cat([p.detach() for p in params])
+        torch.testing.assert_close(flat, ref, rtol=1e-6, atol=1e-6)
+        for i, f in enumerate(flags_host):
+            seg = slice(layout.offsets[i], layout.offsets[i] + NUMELS[i])
+            if f:
+                assert torch.equal(shadow[seg], flat[seg].to(torch.bfloat16))
+            else:
+                assert torch.equal(shadow[seg], untouched[seg])  # fp32 tensors have no shadow copy to keep
+
+
 def test_gather_and_metric(dev):
     from distributed_learning_simulator_b200.ops import sgd as S
 

@@ -87,3 +87,40 @@ def test_layout_with_channels_last_segments():
     plain = ParameterLayout.from_dict(ref)
     assert plain != layout and plain.formats == [0, 0, 0, 0]
     assert ParameterLayout.from_dict(util.get_parameter_dict()) == layout
+
+
+def test_bf16_shadow_keeps_the_fp32_arena_as_master():
+    """ModelUtil.enable_shadow: matrices become bf16 views of the shadow arena, every public
+    accessor still speaks fp32, loads refresh the shadow, disable restores plain fp32 views."""
+    import torch
+
+    from distributed_learning_simulator_b200.engine.model_util import ModelUtil
+    from distributed_learning_simulator_b200 import load_config_from_dict
+
+    torch.manual_seed(0)
+    config = load_config_from_dict({"dataset_name": "MNIST", "model_name": "LeNet5", "distributed_algorithm": "fed_avg",
+                                    "worker_number": 1, "round": 1, "epoch": 1, "log_level": "WARNING",
+                                    "dataset_kwargs": {"train_size": 64, "test_size": 32}})
+    model = config.create_trainer().model
+    util = ModelUtil(model)
+    flat = util.flatten_parameters(with_grad=False)
+    before = {k: v.clone() for k, v in util.get_parameter_dict().items()}
+    shadow = util.enable_shadow()
+    assert shadow.dtype == torch.bfloat16 and shadow.numel() == flat.numel() and util.is_flat()
+    flags = dict(zip(util.layout.names, util.shadow_flags()))
+    assert sum(flags.values()) >= 2
+    for name, p in model.named_parameters():
+        assert p.dtype == (torch.bfloat16 if flags[name] else torch.float32), name
+        assert not flags[name] or (p.dim() >= 2 and p.data_ptr() % 16 == 0)
+    after = util.get_parameter_dict()
+    assert all(v.dtype == torch.float32 and torch.equal(v, before[k]) for k, v in after.items())
+    util.load_parameter_dict({k: v + 1 for k, v in before.items()})
+    assert torch.equal(shadow, flat.to(torch.bfloat16))
+    assert torch.allclose(util.get_parameter_list(), torch.cat([(v + 1).reshape(-1) for v in before.values()]))
+    x = torch.randn(4, 1, 28, 28)
+    with torch.autocast("cpu", dtype=torch.bfloat16):
+        out = model(x)
+    assert out.shape == (4, 10)
+    util.disable_shadow()
+    assert all(p.dtype == torch.float32 for p in model.parameters()) and util.is_flat()
+    assert util.enable_shadow().data_ptr() == shadow.data_ptr()  # same storage: captured graphs stay valid
