@@ -27,10 +27,6 @@ from .log import get_logger
 from .ml_type import ExecutorHookPoint, MachineLearningPhase, StopExecutingException
 from .tensor import TensorDict
 
-# a hook may own the optimizer step (sign_SGD applies the server's majority vote), so the scheduler
-# can legitimately tick without torch having seen optimizer.step()
-warnings.filterwarnings("ignore", message=r"Detected call of `lr_scheduler\.step\(\)` before")
-
 
 class Trainer(ModelExecutor):
     def __init__(self, model: nn.Module, dataset_collection: DatasetCollection, hyper_parameter: HyperParameter,
@@ -149,10 +145,15 @@ class Trainer(ModelExecutor):
                 self.exec_hooks(ExecutorHookPoint.AFTER_FORWARD, executor=self, epoch=epoch, batch_index=batch_index)
                 loss.backward()
                 if self.has_hook(ExecutorHookPoint.OPTIMIZER_STEP):
+                    # the hook owns the update (sign_SGD applies the server's majority vote), so the
+                    # scheduler legitimately ticks without torch having seen optimizer.step()
                     self.exec_hooks(ExecutorHookPoint.OPTIMIZER_STEP, executor=self)
+                    with warnings.catch_warnings():
+                        warnings.simplefilter("ignore", UserWarning)
+                        scheduler.step()
                 else:
                     optimizer.step()
-                scheduler.step()
+                    scheduler.step()
                 self._metric.add_batch(loss, output, batch.targets)
                 self.exec_hooks(ExecutorHookPoint.AFTER_BATCH, executor=self, epoch=epoch, batch_index=batch_index,
                                 batch_size=batch.batch_size)

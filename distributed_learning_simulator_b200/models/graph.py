@@ -9,6 +9,7 @@ from typing import Any
 import torch
 from torch import nn
 
+from ..ops import graph as graph_ops
 from .registry import register_model
 
 
@@ -33,13 +34,9 @@ class GCNConv(MessagePassing):
         self.bias = nn.Parameter(torch.zeros(out_channels)) if bias else None
 
     def forward(self, x: torch.Tensor, edge_index: torch.Tensor, *args: Any, **kwargs: Any) -> torch.Tensor:
-        n = x.shape[0]
         h = self.lin(x)
-        ei, w = gcn_norm(edge_index, n, h.dtype)
-        out = torch.zeros_like(h).index_add_(0, ei[1], h[ei[0]] * w.unsqueeze(-1))
-        if self.bias is not None:
-            out = out + self.bias
-        return out
+        # normalisation + neighbour sum + bias: csrc/graph.cu on a GPU, the index_add_ oracle on CPU
+        return graph_ops.gcn_aggregate(h, edge_index, self.bias)
 
 
 class _GCN(nn.Module):

@@ -22,6 +22,7 @@ from typing import Any, Callable
 
 import torch
 
+from ..ops import graph as graph_ops
 from ..engine.dataset import GraphDatasetUtil, coalesce, index_to_mask, mask_to_index
 from ..engine.log import get_logger
 from ..engine.ml_type import MachineLearningPhase
@@ -226,37 +227,34 @@ class GraphWorker(AggregationWorker):
             return None
         self.__old_edge_index = args[1]
         n_id = self.n_id
-        local = self._on_device(self.local_node_mask, n_id.device)[n_id]
         ei = args[1]
-        keep = local[ei[0]] & local[ei[1]]
+        # K13: endpoints are looked up through n_id and the kept edges compacted in order on the device
+        kept = graph_ops.filter_edges(ei, self._on_device(self.local_node_mask, n_id.device), n_id)
         if module_index > 0:
             x = args[0]
             cnt = int(self._on_device(self.training_boundary_mask, n_id.device)[n_id].sum().item())
             self._skipped_embedding_bytes += x.shape[1] * x.element_size() * cnt
-        return (args[0], ei[:, keep], *args[2:]), kwargs
+        return (args[0], kept, *args[2:]), kwargs
 
     def training_boundary_feature(self, x: torch.Tensor) -> tuple | None:
         n_id = self.n_id
         assert x.shape[0] == n_id.shape[0]
-        rows = self._on_device(self.training_boundary_mask, n_id.device)[n_id].nonzero(as_tuple=False).view(-1)
+        # K13 node select + K14 row gather
+        rows, ids = graph_ops.select_nodes(n_id, self._on_device(self.training_boundary_mask, n_id.device))
         if rows.numel() == 0:
             return None
-        return x.index_select(0, rows).detach(), n_id[rows]
+        return graph_ops.gather_rows(x, rows), ids
 
     def _get_cross_device_embedding(self, embedding_indices: Any, embedding: torch.Tensor | None,
                                     x: torch.Tensor) -> torch.Tensor:
         n_id = self.n_id
-        foreign = ~self._on_device(self.training_node_mask, n_id.device)[n_id]
-        new_x = torch.where(foreign.unsqueeze(-1), torch.zeros_like(x), x)
-        if embedding is None or len(embedding_indices) == 0:
-            return new_x if bool(foreign.any()) else x
-        ids = torch.as_tensor(embedding_indices, dtype=torch.long, device=n_id.device)
-        order = torch.argsort(ids)
-        pos = torch.searchsorted(ids[order], n_id).clamp(max=ids.numel() - 1)
-        hit = (ids[order][pos] == n_id) & foreign
-        rows = hit.nonzero(as_tuple=False).view(-1)
-        new_x = new_x.index_copy(0, rows, embedding.to(x.device, non_blocking=True)[order[pos[rows]]].to(x.dtype))
-        return new_x
+        train_mask = self._on_device(self.training_node_mask, n_id.device)
+        ids = None
+        if embedding is not None and len(embedding_indices) != 0:
+            ids = torch.as_tensor(embedding_indices, dtype=torch.long, device=n_id.device)
+            embedding = embedding.to(x.device, non_blocking=True)
+        # K14: foreign rows take the received embedding of that node (zero when nobody sent one)
+        return graph_ops.halo_merge(x, n_id, train_mask, ids, embedding if ids is not None else None)
 
     def _record_embedding_size(self, module: torch.nn.Module, args: Any, kwargs: Any,
                                module_index: int) -> tuple | None:

@@ -155,6 +155,37 @@ int dls_dropout_mask(const float* in, long long n, float keep_prob, uint64_t see
 int dls_block_sqdiff(const float* cur, const float* prev, const long long* tensor_offsets,
                      const int32_t* block_of_tensor, int n_tensors, int n_blocks, double* scores, void* stream);
 
+/* ---- graph family: fed_gnn / fed_gcn / fed_aas (reference: worker/graph_worker.py:205-216,
+ *      252-269, 271-321) ------------------------------------------------------ */
+/* Ordered (stable) compaction of index pairs.  Pair i is kept iff mask[m(a[i])] && (b == NULL ||
+ * mask[m(b[i])]) && Bernoulli(keep_prob; Philox(seed, i)), with m(v) = n_id ? n_id[v] : v.
+ * out_a / out_b / out_pos (each may be NULL except out_a; out_b iff b) receive the kept values and
+ * their original positions, *count (device) the number kept.  scratch: device ints,
+ * dls_index_compact_scratch_ints(n) of them.  Two launches. */
+long long dls_index_compact_scratch_ints(long long n);
+int dls_index_compact(const long long* a, const long long* b, long long n, const long long* n_id,
+                      const uint8_t* mask, float keep_prob, unsigned long long seed, long long* out_a,
+                      long long* out_b, long long* out_pos, long long* count, int* scratch, void* stream);
+/* out[k, :] = x[rows[k], :]; rows are row_bytes wide (a multiple of 4).  `out` may be a peer-mapped
+ * buffer: the boundary embeddings are then written straight into the consumer GPU's memory. */
+int dls_row_gather(const void* x, const long long* rows, long long n_rows, long long row_bytes, void* out,
+                   void* stream);
+/* Halo merge.  Forward (foreign_in == NULL): row r with g = n_id[r] is copied from x when
+ * train_mask[g], else from emb[perm[j]] where sorted_ids[j] == g, else zero-filled; foreign_out[r]
+ * (may be NULL) records which rows were foreign.  Backward (foreign_in != NULL): out[r] = foreign_in[r]
+ * ? 0 : x[r]. */
+int dls_halo_merge(const void* x, const long long* n_id, long long n_rows, long long row_bytes,
+                   const uint8_t* train_mask, const long long* sorted_ids, const long long* perm, long long n_ids,
+                   const void* emb, const uint8_t* foreign_in, uint8_t* foreign_out, void* out, void* stream);
+/* GCN normalisation and aggregation: dinv[i] = (1 + in-degree(i))^-1/2 (deg_scratch: n_nodes ints),
+ * out = D^-1/2 (A + I) D^-1/2 h (+ bias) with A given as COO (from[e] -> to[e]); fp32 vector
+ * reductions, so the sum order over a node's neighbours is not fixed. */
+int dls_gcn_dinv(const long long* dst, long long n_edges, long long n_nodes, int* deg_scratch, float* dinv,
+                 void* stream);
+int dls_gcn_aggregate(const float* h, const long long* from, const long long* to, long long n_edges,
+                      long long n_nodes, int channels, const float* dinv, const float* bias, float* out,
+                      void* stream);
+
 #ifdef __cplusplus
 }
 #endif
