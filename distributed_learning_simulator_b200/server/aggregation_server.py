@@ -40,6 +40,13 @@ class AggregationServer(Server):
         self.__early_stop = self.config.algorithm_kwargs.get("early_stop", False)
         if self.__early_stop:
             get_logger().warning("stop early")
+        # extension over the reference (which only warm-starts from ``global_model_path``,
+        # aggregation_server.py:43-52): round-counter checkpoints and resume
+        self.__checkpoint_interval = int(self.config.algorithm_kwargs.get("checkpoint_interval", 0) or 0)
+        self.__resumed_parameter: TensorDict | None = None
+        resume_from = self.config.algorithm_kwargs.get("resume_from", None)
+        if resume_from:
+            self.__resume(resume_from)
 
     @property
     def early_stop(self) -> bool:
@@ -53,7 +60,37 @@ class AggregationServer(Server):
     def round_number(self) -> int:
         return self._round_number
 
+    # ---- checkpoint / resume (extension) ----------------------------------------------------------
+    @staticmethod
+    def checkpoint_path(save_dir: str) -> str:
+        return os.path.join(save_dir, "server", "checkpoint.pk")
+
+    def __resume(self, path: str) -> None:
+        if os.path.isdir(path):
+            path = self.checkpoint_path(path)
+        with open(path, "rb") as f:
+            state = pickle.load(f)
+        self._round_number = int(state["round"]) + 1
+        self.__stat = {int(k): v for k, v in state["stat"].items()}
+        self.__plateau, self.__max_acc = state["plateau"], state["max_acc"]
+        self.__best_acc_saved = state["best_acc_saved"]
+        self.__resumed_parameter = state["parameter"]
+        get_logger().warning("resume from %s: continue with round %d of %d", path, self._round_number,
+                             self.config.round)
+
+    def __write_checkpoint(self, parameter: TensorDict) -> None:
+        state = {"round": self._round_number, "stat": self.__stat, "plateau": self.__plateau,
+                 "max_acc": self.__max_acc, "best_acc_saved": self.__best_acc_saved,
+                 "parameter": dict(tensor_to(dict(parameter), device="cpu"))}
+        path = self.checkpoint_path(self.config.save_dir)
+        os.makedirs(os.path.dirname(path), exist_ok=True)
+        with open(path + ".tmp", "wb") as f:
+            pickle.dump(state, f)
+        os.replace(path + ".tmp", path)  # a crash mid-write leaves the previous checkpoint intact
+
     def _get_init_model(self) -> TensorDict:
+        if self.__resumed_parameter is not None:
+            return self.__resumed_parameter
         init_global_model_path = self.config.algorithm_kwargs.get("global_model_path", None)
         if init_global_model_path is not None:
             with open(os.path.join(init_global_model_path), "rb") as f:
@@ -69,8 +106,13 @@ class AggregationServer(Server):
 
     def _before_start(self) -> None:
         if self.config.distribute_init_parameters:
+            other_data: dict = {"init": True}
+            if self.__resumed_parameter is not None:
+                other_data["resume_round"] = self._round_number  # workers continue their round counter
             self._send_result(ParameterMessage(in_round=True, parameter=self._get_init_model(),
-                                               other_data={"init": True}))
+                                               other_data=other_data))
+        else:
+            assert self.__resumed_parameter is None, "resume_from needs distribute_init_parameters"
 
     def _server_exit(self) -> None:
         self.__algorithm.exit()
@@ -99,7 +141,7 @@ class AggregationServer(Server):
         assert isinstance(result, ParameterMessage)
         if self.need_init_performance:
             assert self.config.distribute_init_parameters
-        if self.need_init_performance and "init" in result.other_data:
+        if self.need_init_performance and "init" in result.other_data and "resume_round" not in result.other_data:
             self._record_compute_stat(result.parameter, keep_performance_logger=False)
             self.__stat[0] = self.__stat.pop(1)
             self._dump_stat()
@@ -111,6 +153,9 @@ class AggregationServer(Server):
             self._record_compute_stat(result.parameter)
         model_path = os.path.join(self.config.save_dir, "aggregated_model", f"round_{self.round_number}.pk")
         self._model_cache.cache_parameter_dict(result.parameter, model_path)
+        if self.__checkpoint_interval > 0 and not result.in_round \
+                and self._round_number % self.__checkpoint_interval == 0:
+            self.__write_checkpoint(result.parameter)
         if result.end_training:
             self.__end_training_sent = True
 

@@ -113,6 +113,8 @@ class AggregationWorker(Client):
         if result.end_training:
             self._force_stop = True
             raise StopExecutingException()
+        if "resume_round" in result.other_data:  # the server continues a check-pointed run
+            self._round_num = int(result.other_data["resume_round"])
         model_path = os.path.join(self.config.save_dir, "aggregated_model", f"round_{self._round_num}.pk")
         match result:
             case ParameterMessage():

@@ -31,3 +31,34 @@ def test_fed_avg_lenet5_cpu(small_overrides, monkeypatch):
         model = pickle.load(f)
     assert sum(v.numel() for v in model.values()) == 61706
     assert all(isinstance(v, torch.Tensor) for v in model.values())
+
+
+def test_round_counter_checkpoint_and_resume(small_overrides, monkeypatch):
+    """Extension over the reference (warm start only): ``checkpoint_interval`` writes
+    server/checkpoint.pk, ``resume_from`` continues with the next round number, the restored
+    global model and the earlier rounds' records."""
+    import pickle
+
+    monkeypatch.setenv("DLS_FORCE_CPU", "1")
+    base = {**small_overrides, "epoch": 1, "worker_number": 2, "learning_rate": 0.05}
+    first = load_config_from_file("fed_avg/mnist.yaml", overrides={
+        **base, "round": 2, "algorithm_kwargs": {"checkpoint_interval": 1}})
+    train(first)
+    res1 = get_last_training_result()
+    ck_path = os.path.join(res1["save_dir"], "server", "checkpoint.pk")
+    with open(ck_path, "rb") as f:
+        ck = pickle.load(f)
+    assert ck["round"] == 2 and sorted(ck["stat"]) == [1, 2]
+    assert sum(v.numel() for v in ck["parameter"].values()) == 61706
+
+    second = load_config_from_file("fed_avg/mnist.yaml", overrides={
+        **base, "round": 4, "algorithm_kwargs": {"resume_from": res1["save_dir"], "checkpoint_interval": 2}})
+    train(second)
+    res2 = get_last_training_result()
+    assert sorted(res2["performance"]) == [1, 2, 3, 4]
+    assert res2["performance"][1] == res1["performance"][1] and res2["performance"][2] == res1["performance"][2]
+    with open(os.path.join(res2["save_dir"], "server", "checkpoint.pk"), "rb") as f:
+        assert pickle.load(f)["round"] == 4
+    # the resumed run really started from the check-pointed model: its first new round is no worse
+    # than an untrained model would be, and workers ran exactly two more rounds
+    assert res2["performance"][3]["test_loss"] < res1["performance"][1]["test_loss"]
