@@ -19,92 +19,10 @@
 // work without padding copies.
 #include <stdlib.h>
 
-#include <cuda.h>
-#include <cuda_bf16.h>
-
-#include "common.cuh"
+#include "tcgen05.cuh"
 #include "../../include/dls_b200.h"
 
 namespace dls {
-
-constexpr int kGemmBlockM = 128;
-// BLOCK_N is a template parameter: 64, 128 or 256 columns per tile (= TMEM columns)
-constexpr int kGemmBlockK = 64;   // 64 bf16 = 128 bytes = one swizzle atom row
-constexpr int kGemmUmmaK = 16;
-constexpr int kGemmStages = 4;
-constexpr int kGemmThreads = 192;
-constexpr uint32_t kBytesA = kGemmBlockM * kGemmBlockK * 2;
-
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-// Bounded wait: a protocol bug must end in a trap (error reported to the host), not a hung GPU.
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    const uint32_t addr = smem_u32(bar);
-    for (uint32_t spins = 0;; ++spins) {
-        uint32_t done;
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(done)
-            : "r"(addr), "r"(parity)
-            : "memory");
-        if (done) return;
-        if (spins > 20000000u) asm volatile("trap;");
-    }
-}
-
-__device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1,
-                                            int c2) {
-    asm volatile(
-        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
-        ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
-        : "memory");
-}
-
-// K-major operand tile in shared memory, 128-byte swizzle: rows are 128 bytes apart, groups of
-// 8 rows 1024 bytes apart (SBO), LBO = 1 (unused for swizzled K-major), descriptor version 1.
-__device__ __forceinline__ uint64_t umma_smem_desc(uint32_t smem_addr) {
-    uint64_t desc = 0;
-    desc |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);   // start address, bits [0,14)
-    desc |= (uint64_t)1 << 16;                          // leading byte offset (>>4), bits [16,30)
-    desc |= (uint64_t)(1024 >> 4) << 32;                // stride byte offset (>>4), bits [32,46)
-    desc |= (uint64_t)1 << 46;                          // descriptor version (Blackwell)
-    desc |= (uint64_t)2 << 61;                          // layout type: SWIZZLE_128B
-    return desc;
-}
-
-// kind::f16 instruction descriptor: D = fp32, A = B = bf16, both K-major, M = 128, N = kBlockN
-template <int kBlockN>
-__device__ __forceinline__ uint32_t umma_instr_desc() {
-    uint32_t d = 0;
-    d |= 1u << 4;                         // c_format: F32
-    d |= 1u << 7;                         // a_format: BF16
-    d |= 1u << 10;                        // b_format: BF16
-    d |= (uint32_t)(kBlockN >> 3) << 17;  // n_dim
-    d |= (uint32_t)(kGemmBlockM >> 4) << 24;  // m_dim
-    return d;
-}
-
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
-                                          uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint64_t* bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
-                 : "memory");
-}
 
 template <int kBlockN>
 struct __align__(1024) GemmSmem {
@@ -116,10 +34,6 @@ struct __align__(1024) GemmSmem {
     uint64_t tmem_empty[2];  // accumulator stage drained, the MMA warp may overwrite it
     uint32_t tmem_base;
 };
-
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
 
 template <int kBlockN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
@@ -292,40 +206,6 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
     }
-}
-
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn get_encode_fn() {
-    static EncodeTiledFn fn = [] {
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
-            q != cudaDriverEntryPointSuccess)
-            p = nullptr;
-        return (EncodeTiledFn)p;
-    }();
-    return fn;
-}
-
-// [batch][rows][k] bf16, k contiguous; box = 64 (k) x box_rows x 1, 128-byte swizzle, zero fill
-static int make_map(CUtensorMap* map, const void* base, int rows, int k, int batch, int box_rows) {
-    EncodeTiledFn encode = get_encode_fn();
-    if (encode == nullptr) return fail_msg("cuTensorMapEncodeTiled is not available from this driver");
-    const cuuint64_t dims[3] = {(cuuint64_t)k, (cuuint64_t)rows, (cuuint64_t)batch};
-    const cuuint64_t strides[2] = {(cuuint64_t)k * 2, (cuuint64_t)rows * (cuuint64_t)k * 2};
-    const cuuint32_t box[3] = {(cuuint32_t)kGemmBlockK, (cuuint32_t)box_rows, 1};
-    const cuuint32_t elem_strides[3] = {1, 1, 1};
-    const CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box,
-                              elem_strides, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) {
-        snprintf(g_last_error, sizeof(g_last_error), "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
-        return -1;
-    }
-    return 0;
 }
 
 }  // namespace dls

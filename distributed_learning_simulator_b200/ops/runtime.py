@@ -60,6 +60,8 @@ _SIGNATURES = {
     "dls_sign_majority": [c_void_p, c_int, c_ll, c_void_p, c_void_p],
     "dls_dropout_mask": [c_void_p, c_ll, c_float, c_u64, c_void_p, c_void_p, c_void_p],
     "dls_block_sqdiff": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p],
+    "dls_subset_gemm_bf16": [c_void_p, c_int, c_void_p, c_int, c_ll, c_ll, c_void_p, c_int, c_int, c_int, c_void_p,
+                             c_int, c_int, c_int, c_int, c_int, c_int, c_void_p],
     "dls_index_compact": [c_void_p, c_void_p, c_ll, c_void_p, c_void_p, c_float, c_u64, c_void_p, c_void_p, c_void_p,
                           c_void_p, c_void_p, c_void_p],
     "dls_row_gather": [c_void_p, c_void_p, c_ll, c_ll, c_void_p, c_void_p],

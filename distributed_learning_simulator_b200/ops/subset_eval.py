@@ -6,14 +6,18 @@ host->device load into the tester, a full eager test inference, offload
 Here the N uploaded models are ``[P]`` rows in HBM and a whole list of coalitions is evaluated
 together:
 
-1. coalition models ``W_s = sum_i r_i^s W_i`` are built by the fused reduce kernel straight
-   into one ``[S, P]`` buffer (no per-coalition tensors, no host round trip);
-2. the test set runs through all S models at once, every matrix product on the hand-written
-   tcgen05 GEMM (``ops.gemm.linear_bf16``, bias and ReLU fused in its epilogue): conv1 is ONE GEMM
-   whose B operand stacks the first-layer filters of all coalitions (the image patches are shared,
-   so the coalition models are never materialised as separate convolutions), conv2 and the three
+1. coalition models ``W_s = sum_i r_i^s W_i`` are NEVER materialised: every layer is one launch of
+   the coalition GEMM (``ops.gemm.subset_linear``, csrc/subset_gemm.cu) whose B-operand producer
+   warps read the members' fp32 layer slices straight from the uploaded arenas, form the weighted
+   sum in registers and write the bf16 tile into the swizzled shared-memory slot the
+   ``tcgen05.mma`` reads; the coalition bias is built in the epilogue the same way.  The only
+   per-chunk host input is the ``[S, N]`` coefficient matrix;
+2. the test set runs through all S coalitions at once: conv1 is ONE GEMM whose N dimension stacks
+   the first-layer filters of all coalitions (the image patches are shared), conv2 and the three
    fully connected layers are one batched launch each with batch = coalition; patch extraction
-   (unfold) and pooling stay in PyTorch;
+   (unfold) and pooling stay in PyTorch.  (``subset_eval_fused: false`` selects the older path
+   that first writes the S models into an ``[S, P]`` buffer with the reduce kernel and then runs
+   ``linear_bf16``);
 3. per-coalition accuracy / loss are reduced on the device and read back once.
 
 The GTG engine's truncation rules are applied afterwards to decide which utilities are
@@ -30,7 +34,7 @@ from ..engine.model_util import as_flat
 from . import runtime
 from .reduce import reduce_rows_f32
 
-STATS = {"batched_calls": 0, "coalitions": 0}
+STATS = {"batched_calls": 0, "coalitions": 0, "fused_layer_launches": 0}
 
 
 def make_batch_evaluator(server: Any, all_worker_data: dict, metric_type: str) -> Any:
@@ -66,6 +70,58 @@ class _LeNet5BatchEvaluator:
         self.device = next(iter(flats.values())).flat.device
         self.max_coalitions = int(server.config.algorithm_kwargs.get("subset_eval_chunk", 32))
         self.pad = int(server.tester.model.conv1.padding[0])
+        self.fused = bool(server.config.algorithm_kwargs.get("subset_eval_fused", True))
+        self.worker_ids = sorted(flats)
+        self.rows = [flats[w].flat for w in self.worker_ids]
+        self.table = runtime.pointer_table(self.rows, self.device)
+        self.index = {name: i for i, name in enumerate(layout.names)}
+
+    def _coefficients(self, coalitions: list[tuple]) -> torch.Tensor:
+        coefs = torch.zeros(len(coalitions), len(self.worker_ids), dtype=torch.float32)
+        column = {w: j for j, w in enumerate(self.worker_ids)}
+        for s, members in enumerate(coalitions):
+            total = sum(self.sizes[w] for w in members)
+            for w in members:
+                coefs[s, column[w]] = self.sizes[w] / total
+        return coefs.pin_memory().to(self.device, non_blocking=True)
+
+    def _layer(self, x: torch.Tensor, coefs: torch.Tensor, name: str, stacked: bool, relu: bool,
+               out_dtype: torch.dtype) -> torch.Tensor:
+        from . import gemm
+
+        wi, bi = self.index[f"{name}.weight"], self.index[f"{name}.bias"]
+        shape = self.layout.shapes[wi]
+        n_layer, k_w = int(shape[0]), int(self.layout.numels[wi]) // int(shape[0])
+        STATS["fused_layer_launches"] += 1
+        return gemm.subset_linear(x, self.rows, self.table, coefs, self.layout.offsets[wi], self.layout.offsets[bi],
+                                  n_layer, k_w, stacked=stacked, relu=relu, out_dtype=out_dtype)
+
+    def _forward_fused(self, x: torch.Tensor, coefs: torch.Tensor) -> torch.Tensor:
+        """Logits [S, B, classes] of all coalitions; no coalition model exists in memory."""
+        F = torch.nn.functional
+        S, B = coefs.shape[0], x.shape[0]
+        w1, w2 = self.index["conv1.weight"], self.index["conv2.weight"]
+        k1, k2 = int(self.layout.shapes[w1][-1]), int(self.layout.shapes[w2][-1])
+        c1, c2_in, c2 = int(self.layout.shapes[w1][0]), int(self.layout.shapes[w2][1]), int(self.layout.shapes[w2][0])
+        hw = x.shape[-1] + 2 * self.pad - k1 + 1
+        cols = F.unfold(x, k1, padding=self.pad).transpose(1, 2).reshape(B * hw * hw, -1)
+        if self.layout.formats[w1]:  # filters stored (o, kh, kw, c): reorder the patch columns to match
+            cols = cols.view(B * hw * hw, -1, k1 * k1).transpose(1, 2).reshape(B * hw * hw, -1)
+        z = self._layer(cols.to(torch.bfloat16), coefs, "conv1", True, True, torch.bfloat16)   # [B*hw*hw, S*c1]
+        h = F.max_pool2d(z.view(B, hw, hw, S * c1).permute(0, 3, 1, 2), 2)                       # [B, S*c1, ., .]
+        hw2 = h.shape[-1] - k2 + 1
+        cols = F.unfold(h.float(), k2).view(B, S, c2_in, k2 * k2, hw2 * hw2)
+        if self.layout.formats[w2]:
+            cols = cols.permute(1, 0, 4, 3, 2)       # [S, B, L, kh*kw, c]: the arena's channels-last filter order
+        else:
+            cols = cols.permute(1, 0, 4, 2, 3)       # [S, B, L, c, kh*kw]
+        cols = cols.reshape(S, B * hw2 * hw2, -1).to(torch.bfloat16)
+        z = self._layer(cols, coefs, "conv2", False, True, torch.bfloat16)                      # [S, B*L, c2]
+        h = z.view(S, B, hw2, hw2, c2).permute(0, 1, 4, 2, 3).reshape(S * B, c2, hw2, hw2)
+        feat = F.max_pool2d(h.float(), 2).reshape(S, B, -1).to(torch.bfloat16)                 # (c, h, w) order
+        z = self._layer(feat, coefs, "fc1", False, True, torch.bfloat16)
+        z = self._layer(z, coefs, "fc2", False, True, torch.bfloat16)
+        return self._layer(z, coefs, "fc3", False, False, torch.float32)
 
     def _coalition_models(self, coalitions: list[tuple]) -> torch.Tensor:
         # rows are padded to 256 bytes: the reduce kernel uses 128-bit accesses
@@ -90,6 +146,15 @@ class _LeNet5BatchEvaluator:
         for start in range(0, len(coalitions), self.max_coalitions):
             chunk = coalitions[start: start + self.max_coalitions]
             S = len(chunk)
+            acc = torch.zeros(S, 3, dtype=torch.float64, device=self.device)
+            if self.fused:
+                coefs = self._coefficients(chunk)
+                for batch in tester._loader(phase):
+                    x, y = batch.inputs[0], batch.targets
+                    logits = self._forward_fused(x, coefs)
+                    self._accumulate(acc, logits, y)
+                self._finish(tester, acc, results)
+                continue
             models = self._coalition_models(chunk)
             p = {name: torch.stack([self.layout.view_of(models[s], i) for s in range(S)])
                  for i, name in enumerate(self.layout.names)}
@@ -99,7 +164,6 @@ class _LeNet5BatchEvaluator:
             b2 = p["conv2.bias"].reshape(S * 16)
             fw = [p[f"fc{j}.weight"].to(torch.bfloat16).contiguous() for j in (1, 2, 3)]
             fb = [p[f"fc{j}.bias"].contiguous() for j in (1, 2, 3)]
-            acc = torch.zeros(S, 3, dtype=torch.float64, device=self.device)
             conv_gemm = bool(self.server.config.algorithm_kwargs.get("subset_eval_conv_gemm", True))
             if conv_gemm:
                 # convolution weights as GEMM operands: conv1 of ALL coalitions is one B matrix
@@ -131,19 +195,28 @@ class _LeNet5BatchEvaluator:
                 z = gemm.linear_bf16(feat, fw[0], fb[0], relu=True, out_dtype=torch.bfloat16)
                 z = gemm.linear_bf16(z, fw[1], fb[1], relu=True, out_dtype=torch.bfloat16)
                 logits = gemm.linear_bf16(z, fw[2], fb[2], relu=False, out_dtype=torch.float32)  # [S, B, classes]
-                loss = F.cross_entropy(logits.reshape(S * B, -1), y.repeat(S), reduction="none").view(S, B).sum(1)
-                correct = (logits.argmax(-1) == y.unsqueeze(0)).sum(1)
-                acc[:, 0] += loss.double()
-                acc[:, 1] += correct.double()
-                acc[:, 2] += B
-            reducer = getattr(tester, "_reducer", None)
-            if reducer is not None:
-                reducer.all_reduce_sum(acc)
-            acc = acc.cpu()
-            for s in range(S):
-                n = max(float(acc[s, 2]), 1.0)
-                metric = {"loss": float(acc[s, 0]) / n, "accuracy": float(acc[s, 1]) / n}
-                results.append(metric[self.metric_type])
-            STATS["batched_calls"] += 1
-            STATS["coalitions"] += S
+                self._accumulate(acc, logits, y)
+            self._finish(tester, acc, results)
         return results
+
+    @staticmethod
+    def _accumulate(acc: torch.Tensor, logits: torch.Tensor, y: torch.Tensor) -> None:
+        S, B = logits.shape[0], logits.shape[1]
+        loss = torch.nn.functional.cross_entropy(logits.reshape(S * B, -1), y.repeat(S),
+                                                 reduction="none").view(S, B).sum(1)
+        correct = (logits.argmax(-1) == y.unsqueeze(0)).sum(1)
+        acc[:, 0] += loss.double()
+        acc[:, 1] += correct.double()
+        acc[:, 2] += B
+
+    def _finish(self, tester: Any, acc: torch.Tensor, results: list[float]) -> None:
+        reducer = getattr(tester, "_reducer", None)
+        if reducer is not None:
+            reducer.all_reduce_sum(acc)
+        acc = acc.cpu()
+        for s in range(acc.shape[0]):
+            n = max(float(acc[s, 2]), 1.0)
+            metric = {"loss": float(acc[s, 0]) / n, "accuracy": float(acc[s, 1]) / n}
+            results.append(metric[self.metric_type])
+        STATS["batched_calls"] += 1
+        STATS["coalitions"] += acc.shape[0]

@@ -155,6 +155,22 @@ int dls_dropout_mask(const float* in, long long n, float keep_prob, uint64_t see
 int dls_block_sqdiff(const float* cur, const float* prev, const long long* tensor_offsets,
                      const int32_t* block_of_tensor, int n_tensors, int n_blocks, double* scores, void* stream);
 
+/* ---- coalition GEMM for the Shapley engines (reference: method/shapley_value/
+ *      shapley_value_algorithm.py:67-76 builds each coalition model on the CPU) -----------------
+ * C[s] = act(A[s] * W_s^T + b_s) with W_s = sum_i coefs[s][i] * W_i built inside the kernel as the
+ * B-operand producer of the tcgen05 GEMM (the coalition model is never written to memory).
+ * worker_ptrs: DEVICE array of n_workers (<= 64) fp32 arena base pointers; the layer's weight
+ * [n_layer][k_w] (row-major) starts at element w_offset of every arena, its bias at bias_offset (-1:
+ * none).  coefs: device fp32 [n_sets][n_workers].  a: bf16 [n_sets or 1][m][k_a], k_a % 8 == 0,
+ * k_a >= k_w (extra columns are ignored).  stacked == 0: c is [n_sets][m][n_layer] (batch = coalition;
+ * a_shared selects one A for all).  stacked != 0: ONE GEMM, c is [m][n_sets * n_layer] (column
+ * block s holds coalition s; A is shared by construction).  ptrs_aligned: every arena base is
+ * 16-byte aligned (enables 128-bit weight loads where w_offset / k_w allow). */
+int dls_subset_gemm_bf16(const void* a, int a_shared, const float* const* worker_ptrs, int n_workers,
+                         long long w_offset, long long bias_offset, const float* coefs, int n_sets, int n_layer,
+                         int stacked, void* c, int out_dtype, int m, int k_a, int k_w, int relu, int ptrs_aligned,
+                         void* stream);
+
 /* ---- graph family: fed_gnn / fed_gcn / fed_aas (reference: worker/graph_worker.py:205-216,
  *      252-269, 271-321) ------------------------------------------------------ */
 /* Ordered (stable) compaction of index pairs.  Pair i is kept iff mask[m(a[i])] && (b == NULL ||

@@ -60,3 +60,49 @@ def test_inference_linear_patch_matches_torch():
     y = model(x)  # autograd path is untouched
     y.sum().backward()
     assert model[0].weight.grad is not None and G.STATS["linear_calls"] - before == 2
+
+
+@pytest.mark.parametrize("case", [
+    # (coalitions, workers, M, n_layer, k_w, weight offset, stacked, bias, relu, out dtype, arena shift)
+    dict(S=5, NW=10, M=300, n=120, k=400, off=2572, stacked=False, bias=True, relu=True, out=torch.bfloat16),
+    dict(S=7, NW=10, M=1000, n=6, k=25, off=0, stacked=True, bias=True, relu=True, out=torch.bfloat16),
+    dict(S=3, NW=4, M=257, n=16, k=150, off=156, stacked=False, bias=True, relu=False, out=torch.float32),
+    dict(S=33, NW=10, M=64, n=10, k=84, off=60856, stacked=False, bias=False, relu=False, out=torch.float32),
+    dict(S=4, NW=3, M=129, n=200, k=136, off=8, stacked=False, bias=True, relu=True, out=torch.float32),
+    dict(S=9, NW=64, M=500, n=40, k=72, off=4, stacked=True, bias=True, relu=False, out=torch.float32),
+    dict(S=2, NW=5, M=130, n=70, k=64, off=3, stacked=False, bias=True, relu=False, out=torch.float32, shift=1),
+])
+@pytest.mark.parametrize("cluster", [2, 1])
+def test_subset_gemm_builds_the_coalition_weights_inside_the_gemm(case, cluster, monkeypatch):
+    """csrc/subset_gemm.cu: the B operand of the tcgen05 GEMM is formed in shared memory as the
+    coalition-weighted sum of the workers' fp32 layer slices (never materialised).  Oracle: fp32
+    einsum of the same slices, rounded to bf16 like the kernel's operand, then a plain matmul."""
+    from distributed_learning_simulator_b200.ops import gemm, runtime
+
+    runtime.require()
+    # 2: CTA pairs share each built tile through DSMEM (default); 1: every CTA builds its own
+    monkeypatch.setenv("DLS_SUBSET_CLUSTER", str(cluster))
+    dev = torch.device("cuda", 0)
+    g = torch.Generator().manual_seed(case["S"] * 131 + case["n"])
+    S, NW, M, n, k = case["S"], case["NW"], case["M"], case["n"], case["k"]
+    total = case["off"] + n * k + n + 13
+    shift = case.get("shift", 0)  # arenas that are only 4-byte aligned take the scalar load path
+    arenas = [torch.randn(total + 4, generator=g).to(dev)[shift: shift + total] for _ in range(NW)]
+    bias_off = case["off"] + n * k if case["bias"] else None
+    member = torch.rand(S, NW, generator=g) < 0.5
+    member[:, 0] |= ~member.any(dim=1)
+    coefs = torch.rand(S, NW, generator=g) * member
+    coefs = (coefs / coefs.sum(dim=1, keepdim=True)).to(dev).contiguous()
+    shared_a = case["stacked"] or S % 2 == 1
+    x = (torch.randn((M, k) if shared_a else (S, M, k), generator=g) * 0.5).to(dev, torch.bfloat16)
+    table = runtime.pointer_table(arenas, dev)
+    before = runtime.launch_count()
+    out = gemm.subset_linear(x, arenas, table, coefs, case["off"], bias_off, n, k, stacked=case["stacked"],
+                             relu=case["relu"], out_dtype=case["out"])
+    torch.cuda.synchronize()
+    assert runtime.launch_count() - before == 1
+    ref = gemm.oracle_subset_linear(x, arenas, coefs, case["off"], bias_off, n, k, stacked=case["stacked"],
+                                    relu=case["relu"])
+    assert out.shape == ref.shape and out.dtype == case["out"]
+    tol = 2e-2 if case["out"] == torch.bfloat16 else 2e-3
+    torch.testing.assert_close(out.float(), ref, rtol=tol, atol=tol)

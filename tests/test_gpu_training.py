@@ -87,28 +87,34 @@ def test_smoke_entry():
 
 
 def test_batched_coalition_evaluator_matches_sequential():
-    """GTG-Shapley on GPU: coalitions evaluated in batched launches (fused reduce + tcgen05 GEMMs)
-    give the same Shapley values as one-by-one evaluation, within the bf16 tolerance."""
+    """GTG-Shapley on GPU: coalitions evaluated in batched launches - the coalition GEMM that builds
+    W_s inside the tcgen05 kernel (default), or the older materialise-then-GEMM path - give the same
+    Shapley values as one-by-one evaluation, within the bf16 tolerance."""
     from distributed_learning_simulator_b200 import load_config_from_dict, train
     from distributed_learning_simulator_b200.ops import subset_eval
     from distributed_learning_simulator_b200.training import get_last_training_result
 
     results = {}
-    for batched in (True, False):
-        before = subset_eval.STATS["coalitions"]
+    modes = {"fused": {"batched_subset_eval": True}, "materialised": {"batched_subset_eval": True,
+                                                                       "subset_eval_fused": False},
+             "sequential": {"batched_subset_eval": False}}
+    for mode, kwargs in modes.items():
+        before = dict(subset_eval.STATS)
         config = load_config_from_dict(_conf(distributed_algorithm="GTG_shapley_value", worker_number=4, round=2,
-                                             epoch=1, learning_rate=0.1,
-                                             algorithm_kwargs={"batched_subset_eval": batched},
+                                             epoch=1, learning_rate=0.1, algorithm_kwargs=kwargs,
                                              dataset_kwargs={"train_size": 1200, "test_size": 2000}))
         train(config)
-        results[batched] = get_last_training_result()
-        used = subset_eval.STATS["coalitions"] - before
-        assert (used > 0) == batched
-    for rnd in (1, 2):
-        a, b = results[True]["sv"][rnd], results[False]["sv"][rnd]
-        assert set(a) == set(b) == {0, 1, 2, 3}
-        for w in a:
-            assert abs(a[w] - b[w]) < 0.02, (rnd, a, b)
-    for rnd in (0, 1, 2):
-        assert abs(results[True]["performance"][rnd]["test_accuracy"]
-                   - results[False]["performance"][rnd]["test_accuracy"]) < 0.02  # two independent trainings
+        results[mode] = get_last_training_result()
+        used = subset_eval.STATS["coalitions"] - before["coalitions"]
+        fused_launches = subset_eval.STATS["fused_layer_launches"] - before["fused_layer_launches"]
+        assert (used > 0) == (mode != "sequential")
+        assert (fused_launches > 0) == (mode == "fused")
+    for mode in ("fused", "materialised"):
+        for rnd in (1, 2):
+            a, b = results[mode]["sv"][rnd], results["sequential"]["sv"][rnd]
+            assert set(a) == set(b) == {0, 1, 2, 3}
+            for w in a:
+                assert abs(a[w] - b[w]) < 0.02, (mode, rnd, a, b)
+        for rnd in (0, 1, 2):
+            assert abs(results[mode]["performance"][rnd]["test_accuracy"]
+                       - results["sequential"]["performance"][rnd]["test_accuracy"]) < 0.02  # independent trainings

@@ -116,6 +116,41 @@ for (bsz, m, n, k) in [(1, 5000, 120, 400), (32, 5000, 120, 400), (32, 5000, 84,
     timed(f"gemm_tcgen05 b={bsz} {m}x{n}x{k}", lambda: G.linear_bf16(a, w_, bias, relu=True, out_dtype=torch.bfloat16),
           bytes_moved=bsz * (m * k + n * k + m * n) * 2, flops=2.0 * bsz * m * n * k, cold=False)
 
+# coalition GEMM: W_s built inside the kernel (cluster pair sharing the tile / one CTA each) against
+# the older two-step path (reduce kernel writes S models, cast, batched GEMM); LeNet-5 fc1 and conv2 shapes
+from distributed_learning_simulator_b200.ops import runtime as RT  # noqa: E402
+
+NW, S_, Pl = 10, 32, 61706
+arenas = [torch.randn(Pl + 6, device=dev)[:Pl] for _ in range(NW)]
+ptable = RT.pointer_table(arenas, dev)
+member = torch.rand(S_, NW) < 0.5
+member[:, 0] |= ~member.any(dim=1)
+coefs = (member.float() / member.float().sum(1, keepdim=True)).to(dev).contiguous()
+for (name, m, n, k, off) in [("fc1", 5000, 120, 400, 2572), ("conv2", 5000 * 100 // 10, 16, 150, 156)]:
+    xa = torch.randn(S_, m, k + (-k) % 8, device=dev).bfloat16()
+    for cl in (2, 1):
+        os.environ["DLS_SUBSET_CLUSTER"] = str(cl)
+        timed(f"subset_gemm {name} S={S_} NW={NW} {m}x{n}x{k} cluster={cl}",
+              lambda: G.subset_linear(xa, arenas, ptable, coefs, off, off + n * k, n, k, relu=True,
+                                      out_dtype=torch.bfloat16),
+              flops=2.0 * S_ * m * n * k, cold=False)
+    os.environ.pop("DLS_SUBSET_CLUSTER")
+    stride = (Pl + 63) // 64 * 64
+    models = torch.empty(S_, stride, device=dev)[:, :Pl]
+
+    def two_step():
+        for s_i in range(S_):
+            sel = [i for i in range(NW) if member[s_i, i]]
+            R.reduce_rows_f32([arenas[i] for i in sel], [1.0 / len(sel)] * len(sel), None, 0.0, 1.0, out=models[s_i],
+                              check_nan=False)
+        w_b = models[:, off: off + n * k].reshape(S_, n, k).to(torch.bfloat16)
+        if k % 8:
+            w_b = torch.nn.functional.pad(w_b, (0, 8 - k % 8))
+        return G.linear_bf16(xa, w_b.contiguous(), models[:, off + n * k: off + n * k + n].contiguous(), relu=True,
+                             out_dtype=torch.bfloat16)
+
+    timed(f"materialise + gemm {name} S={S_} NW={NW} {m}x{n}x{k}", two_step, flops=2.0 * S_ * m * n * k, cold=False)
+
 out_path = os.environ.get("OUT", "gpurun_out/kernel_times.json")
 os.makedirs(os.path.dirname(out_path), exist_ok=True)
 with open(out_path, "w") as f:
