@@ -71,9 +71,13 @@ def test_inference_linear_patch_matches_torch():
     dict(S=4, NW=3, M=129, n=200, k=136, off=8, stacked=False, bias=True, relu=True, out=torch.float32),
     dict(S=9, NW=64, M=500, n=40, k=72, off=4, stacked=True, bias=True, relu=False, out=torch.float32),
     dict(S=2, NW=5, M=130, n=70, k=64, off=3, stacked=False, bias=True, relu=False, out=torch.float32, shift=1),
+    dict(S=3, NW=6, M=5000, n=120, k=400, off=12, stacked=False, bias=True, relu=True, out=torch.float32),
+    dict(S=2, NW=4, M=700, n=48, k=600, off=16, stacked=False, bias=True, relu=False, out=torch.float32),  # K > 512
+    dict(S=6, NW=8, M=40000, n=6, k=25, off=0, stacked=True, bias=True, relu=True, out=torch.bfloat16),
 ])
+@pytest.mark.parametrize("stationary", [1, 0])
 @pytest.mark.parametrize("cluster", [2, 1])
-def test_subset_gemm_builds_the_coalition_weights_inside_the_gemm(case, cluster, monkeypatch):
+def test_subset_gemm_builds_the_coalition_weights_inside_the_gemm(case, cluster, stationary, monkeypatch):
     """csrc/subset_gemm.cu: the B operand of the tcgen05 GEMM is formed in shared memory as the
     coalition-weighted sum of the workers' fp32 layer slices (never materialised).  Oracle: fp32
     einsum of the same slices, rounded to bf16 like the kernel's operand, then a plain matmul."""
@@ -82,6 +86,8 @@ def test_subset_gemm_builds_the_coalition_weights_inside_the_gemm(case, cluster,
     runtime.require()
     # 2: CTA pairs share each built tile through DSMEM (default); 1: every CTA builds its own
     monkeypatch.setenv("DLS_SUBSET_CLUSTER", str(cluster))
+    # 1: the built tile stays resident over a run of M tiles (K <= 512); 0: rebuilt for every output tile
+    monkeypatch.setenv("DLS_SUBSET_STATIONARY", str(stationary))
     dev = torch.device("cuda", 0)
     g = torch.Generator().manual_seed(case["S"] * 131 + case["n"])
     S, NW, M, n, k = case["S"], case["NW"], case["M"], case["n"], case["k"]
