@@ -29,8 +29,11 @@ class ShapleyValue:
         if not key:
             return self.last_round_metric
         if key not in self._cache:
-            assert self.metric_fun is not None
-            self._cache[key] = float(self.metric_fun(tuple(sorted(key))))
+            if self.batch_metric_fun is not None:  # same evaluator (and rounding) as the prefetched values
+                self._cache[key] = float(self.batch_metric_fun([tuple(sorted(key))])[0])
+            else:
+                assert self.metric_fun is not None
+                self._cache[key] = float(self.metric_fun(tuple(sorted(key))))
             self.evaluations += 1
         return self._cache[key]
 

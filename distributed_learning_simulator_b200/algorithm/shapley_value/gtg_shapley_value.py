@@ -25,8 +25,10 @@ from .base import ShapleyValue
 class GTGShapleyValue(ShapleyValue):
     def __init__(self, players, last_round_metric: float = 0.0, eps: float = 0.001,
                  round_trunc_threshold: float = 0.001, converge_min: int | None = None, last_k: int = 10,
-                 converge_criteria: float = 0.05, max_percentage: float = 0.8, seed: int = 0, **kwargs) -> None:
+                 converge_criteria: float = 0.05, max_percentage: float = 0.8, seed: int = 0,
+                 speculative_prefetch: bool = True, **kwargs) -> None:
         super().__init__(players, last_round_metric, **kwargs)
+        self.speculative_prefetch = speculative_prefetch
         self.eps = eps
         self.round_trunc_threshold = round_trunc_threshold
         self.converge_min = converge_min if converge_min is not None else max(30, self.player_number)
@@ -72,6 +74,14 @@ class GTGShapleyValue(ShapleyValue):
             # level-2 prefixes of the whole sweep are needed unless truncated at level 1: batch them
             self.prefetch([perm[:2] for perm in sweep
                            if abs(v_all - self.metric(perm[:1])) >= self.eps and n >= 2])
+            if self.batch_metric_fun is not None and self.speculative_prefetch:
+                # With a batched evaluator one more coalition costs a slice of a launch, while a cache miss
+                # inside the walk below costs a launch of its own plus a host read: evaluate every prefix of
+                # the sweep whose permutation survived level 2 up front.  The truncation rule still decides
+                # which utilities are *used*, so the values are those of the sequential walk.
+                alive = [perm for perm in sweep if n >= 3 and abs(v_all - self.metric(perm[:1])) >= self.eps
+                         and abs(v_all - self.metric(perm[:2])) >= self.eps]
+                self.prefetch([perm[:j] for perm in alive for j in range(3, n + 1)])
             for perm in sweep:
                 marginal = np.zeros(n)
                 prev = self.last_round_metric
@@ -87,6 +97,8 @@ class GTGShapleyValue(ShapleyValue):
         best = self._best_subset(self._cache.keys())
         if best:
             members = tuple(sorted(best))
+            if len(members) <= 6:
+                self.prefetch([c for c in self.powerset(members) if c])
             # restrict to the best coalition; unseen sub-coalitions fall back to evaluation
             self.shapley_values_S = self.exact_shapley(members, self.metric) if len(members) <= 6 else {
                 p: self.shapley_values[p] for p in members}

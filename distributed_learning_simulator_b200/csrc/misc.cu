@@ -141,3 +141,65 @@ extern "C" int dls_block_sqdiff(const float* cur, const float* prev, const long 
     DLS_LAUNCHED("block_sqdiff_kernel");
     return 0;
 }
+
+// ---- grouped im2col for the coalition evaluator -----------------------------------------------------
+// x: [B][H][W][G*C] (channels-last activations of G coalitions, C channels each), valid k x k windows.
+// cols: [G][B*OH*OW][k_pad]; column order (kh, kw, c) when channels_last_k (the arena stores 4-D filters
+// channels-last) else (c, kh, kw); columns past C*k*k are zero.  One thread per (g, b, oh, ow, kh, kw).
+// The reference has no counterpart (it runs each coalition through an eager torch convolution,
+// server/server.py:40-55); torch's unfold took 80 % of the batched evaluator before this kernel.
+namespace dls {
+template <typename T>
+__global__ void __launch_bounds__(256)
+im2col_grouped_kernel(const T* __restrict__ x, int batch, int height, int width, int groups, int channels, int k,
+                      int k_pad, int channels_last_k, T* __restrict__ cols) {
+    const int oh_n = height - k + 1, ow_n = width - k + 1;
+    const long long rows = (long long)batch * oh_n * ow_n;
+    const long long total = (long long)groups * rows * k * k;
+    const int kk = k * k;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+         t += (long long)gridDim.x * blockDim.x) {
+        const int tap = (int)(t % kk);
+        const long long row_g = t / kk;           // g * rows + row
+        const long long row = row_g % rows;
+        const int g = (int)(row_g / rows);
+        const int ow = (int)(row % ow_n), oh = (int)((row / ow_n) % oh_n);
+        const int b = (int)(row / ((long long)ow_n * oh_n));
+        const int kh = tap / k, kw = tap - kh * k;
+        const T* src = x + (((long long)b * height + oh + kh) * width + ow + kw) * ((long long)groups * channels) +
+                       (long long)g * channels;
+        T* dst_row = cols + row_g * k_pad;
+        if (channels_last_k) {
+            T* dst = dst_row + tap * channels;
+            if (sizeof(T) == 2 && (channels & 1) == 0 && (k_pad & 1) == 0) {
+                const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src);
+                uint32_t* d32 = reinterpret_cast<uint32_t*>(dst);
+                for (int c = 0; c < channels / 2; ++c) d32[c] = s32[c];
+            } else {
+                for (int c = 0; c < channels; ++c) dst[c] = src[c];
+            }
+        } else {
+            for (int c = 0; c < channels; ++c) dst_row[c * kk + tap] = src[c];
+        }
+        if (tap == kk - 1)
+            for (int j = channels * kk; j < k_pad; ++j) dst_row[j] = T(0);
+    }
+}
+}  // namespace dls
+
+extern "C" int dls_im2col_grouped(const void* x, int elem_bytes, int batch, int height, int width, int groups,
+                                  int channels, int k, int k_pad, int channels_last_k, void* cols, void* stream) {
+    if (batch < 1 || groups < 1 || channels < 1 || k < 1 || height < k || width < k || k_pad < channels * k * k)
+        return dls::fail_msg("dls_im2col_grouped: bad shape");
+    if (elem_bytes != 2 && elem_bytes != 4) return dls::fail_msg("dls_im2col_grouped: 2- or 4-byte elements");
+    const long long total = (long long)groups * batch * (height - k + 1) * (width - k + 1) * k * k;
+    const int grid = dls::grid_for(total, 256, 16);
+    if (elem_bytes == 2)
+        dls::im2col_grouped_kernel<uint16_t><<<grid, 256, 0, (cudaStream_t)stream>>>(
+            (const uint16_t*)x, batch, height, width, groups, channels, k, k_pad, channels_last_k, (uint16_t*)cols);
+    else
+        dls::im2col_grouped_kernel<uint32_t><<<grid, 256, 0, (cudaStream_t)stream>>>(
+            (const uint32_t*)x, batch, height, width, groups, channels, k, k_pad, channels_last_k, (uint32_t*)cols);
+    DLS_LAUNCHED("im2col_grouped_kernel");
+    return 0;
+}

@@ -21,6 +21,7 @@ from typing import Any, Iterable, Type
 from ...algorithm.shapley_value import GTGShapleyValue, HierarchicalShapleyValue, MultiRoundShapleyValue
 from ...engine.log import get_logger
 from ..common_import import AggregationServer, FedAVGAlgorithm, Message
+from ...utils import tracing
 
 
 class ShapleyValueAlgorithm(FedAVGAlgorithm):
@@ -47,7 +48,10 @@ class ShapleyValueAlgorithm(FedAVGAlgorithm):
         return sorted(self._all_worker_data.keys())
 
     def _engine_kwargs(self) -> dict:
-        return {"seed": self.config.reproducible_env_config.seed}
+        kwargs = {"seed": self.config.reproducible_env_config.seed}
+        if "speculative_prefetch" in self.config.algorithm_kwargs:
+            kwargs["speculative_prefetch"] = bool(self.config.algorithm_kwargs["speculative_prefetch"])
+        return kwargs
 
     def aggregate_worker_data(self) -> Message:
         if self.sv_algorithm is None:
@@ -61,7 +65,8 @@ class ShapleyValueAlgorithm(FedAVGAlgorithm):
         assert self.sv_algorithm is not None
         self.sv_algorithm.set_metric_function(self._get_subset_metric)
         self.sv_algorithm.set_batch_metric_function(self._batch_evaluator())
-        self.sv_algorithm.compute(round_number=self._server.round_number)
+        with tracing.phase("shapley"):
+            self.sv_algorithm.compute(round_number=self._server.round_number)
         self.subset_evaluations += self.sv_algorithm.evaluations
         self.sv_algorithm.evaluations = 0
         self.shapley_values[self._server.round_number] = copy.deepcopy(

@@ -62,6 +62,7 @@ _SIGNATURES = {
     "dls_block_sqdiff": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p],
     "dls_subset_gemm_bf16": [c_void_p, c_int, c_void_p, c_int, c_ll, c_ll, c_void_p, c_int, c_int, c_int, c_void_p,
                              c_int, c_int, c_int, c_int, c_int, c_int, c_void_p],
+    "dls_im2col_grouped": [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p],
     "dls_index_compact": [c_void_p, c_void_p, c_ll, c_void_p, c_void_p, c_float, c_u64, c_void_p, c_void_p, c_void_p,
                           c_void_p, c_void_p, c_void_p],
     "dls_row_gather": [c_void_p, c_void_p, c_ll, c_ll, c_void_p, c_void_p],

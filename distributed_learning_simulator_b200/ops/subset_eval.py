@@ -34,7 +34,32 @@ from ..engine.model_util import as_flat
 from . import runtime
 from .reduce import reduce_rows_f32
 
-STATS = {"batched_calls": 0, "coalitions": 0, "fused_layer_launches": 0}
+STATS = {"batched_calls": 0, "coalitions": 0, "fused_layer_launches": 0, "calls": 0, "seconds": 0.0}
+
+
+_PROFILE = __import__("os").environ.get("DLS_SUBSET_PROFILE", "0") == "1"
+STAGE_MS: dict = {}
+
+
+class _StageTimer:
+    """CUDA-event stage timing of the fused forward (DLS_SUBSET_PROFILE=1; synchronises, so profiling only)."""
+
+    def __init__(self) -> None:
+        self.events = [("start", self._event())]
+
+    @staticmethod
+    def _event() -> torch.cuda.Event:
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        return e
+
+    def __call__(self, name: str) -> None:
+        self.events.append((name, self._event()))
+
+    def flush(self) -> None:
+        torch.cuda.synchronize()
+        for (_, a), (name, b) in zip(self.events, self.events[1:]):
+            STAGE_MS[name] = STAGE_MS.get(name, 0.0) + a.elapsed_time(b)
 
 
 def make_batch_evaluator(server: Any, all_worker_data: dict, metric_type: str) -> Any:
@@ -71,6 +96,9 @@ class _LeNet5BatchEvaluator:
         self.max_coalitions = int(server.config.algorithm_kwargs.get("subset_eval_chunk", 32))
         self.pad = int(server.tester.model.conv1.padding[0])
         self.fused = bool(server.config.algorithm_kwargs.get("subset_eval_fused", True))
+        # the fused path walks the test set in large slices (GEMM M dimension = samples x positions)
+        self.eval_batch = int(server.config.algorithm_kwargs.get("subset_eval_batch", 1024))
+        self._patch_cache: dict = {}
         self.worker_ids = sorted(flats)
         self.rows = [flats[w].flat for w in self.worker_ids]
         self.table = runtime.pointer_table(self.rows, self.device)
@@ -96,32 +124,46 @@ class _LeNet5BatchEvaluator:
         return gemm.subset_linear(x, self.rows, self.table, coefs, self.layout.offsets[wi], self.layout.offsets[bi],
                                   n_layer, k_w, stacked=stacked, relu=relu, out_dtype=out_dtype)
 
-    def _forward_fused(self, x: torch.Tensor, coefs: torch.Tensor) -> torch.Tensor:
+    def _forward_fused(self, x: torch.Tensor, coefs: torch.Tensor, cache_key: Any = None) -> torch.Tensor:
         """Logits [S, B, classes] of all coalitions; no coalition model exists in memory."""
+        from . import misc
+
         F = torch.nn.functional
+        mark = _StageTimer() if _PROFILE else None
         S, B = coefs.shape[0], x.shape[0]
         w1, w2 = self.index["conv1.weight"], self.index["conv2.weight"]
         k1, k2 = int(self.layout.shapes[w1][-1]), int(self.layout.shapes[w2][-1])
         c1, c2_in, c2 = int(self.layout.shapes[w1][0]), int(self.layout.shapes[w2][1]), int(self.layout.shapes[w2][0])
         hw = x.shape[-1] + 2 * self.pad - k1 + 1
-        cols = F.unfold(x, k1, padding=self.pad).transpose(1, 2).reshape(B * hw * hw, -1)
-        if self.layout.formats[w1]:  # filters stored (o, kh, kw, c): reorder the patch columns to match
-            cols = cols.view(B * hw * hw, -1, k1 * k1).transpose(1, 2).reshape(B * hw * hw, -1)
-        z = self._layer(cols.to(torch.bfloat16), coefs, "conv1", True, True, torch.bfloat16)   # [B*hw*hw, S*c1]
+        cols = self._patch_cache.get(cache_key) if cache_key is not None else None
+        if cols is None:  # first-layer patches do not depend on the coalition: built once per test slice
+            cols = F.unfold(x, k1, padding=self.pad).transpose(1, 2).reshape(B * hw * hw, -1)
+            if self.layout.formats[w1]:  # filters stored (o, kh, kw, c): reorder the patch columns to match
+                cols = cols.view(B * hw * hw, -1, k1 * k1).transpose(1, 2).reshape(B * hw * hw, -1)
+            cols = torch.nn.functional.pad(cols.to(torch.bfloat16), (0, (-cols.shape[1]) % 8)).contiguous()
+            if cache_key is not None:
+                self._patch_cache[cache_key] = cols
+        if mark: mark("patches1")
+        z = self._layer(cols, coefs, "conv1", True, True, torch.bfloat16)                        # [B*hw*hw, S*c1]
+        if mark: mark("conv1_gemm")
         h = F.max_pool2d(z.view(B, hw, hw, S * c1).permute(0, 3, 1, 2), 2)                       # [B, S*c1, ., .]
+        if mark: mark("pool1")
         hw2 = h.shape[-1] - k2 + 1
-        cols = F.unfold(h.float(), k2).view(B, S, c2_in, k2 * k2, hw2 * hw2)
-        if self.layout.formats[w2]:
-            cols = cols.permute(1, 0, 4, 3, 2)       # [S, B, L, kh*kw, c]: the arena's channels-last filter order
-        else:
-            cols = cols.permute(1, 0, 4, 2, 3)       # [S, B, L, c, kh*kw]
-        cols = cols.reshape(S, B * hw2 * hw2, -1).to(torch.bfloat16)
+        # second-layer patches of all coalitions in one pass (csrc/misc.cu): [S, B*L, K], filter order of the arena
+        cols = misc.im2col_grouped(h.permute(0, 2, 3, 1).contiguous(), S, k2, bool(self.layout.formats[w2]))
+        if mark: mark("im2col2")
         z = self._layer(cols, coefs, "conv2", False, True, torch.bfloat16)                      # [S, B*L, c2]
+        if mark: mark("conv2_gemm")
         h = z.view(S, B, hw2, hw2, c2).permute(0, 1, 4, 2, 3).reshape(S * B, c2, hw2, hw2)
-        feat = F.max_pool2d(h.float(), 2).reshape(S, B, -1).to(torch.bfloat16)                 # (c, h, w) order
+        feat = F.max_pool2d(h, 2).reshape(S, B, -1)                                             # (c, h, w) order
+        if mark: mark("pool2")
         z = self._layer(feat, coefs, "fc1", False, True, torch.bfloat16)
         z = self._layer(z, coefs, "fc2", False, True, torch.bfloat16)
-        return self._layer(z, coefs, "fc3", False, False, torch.float32)
+        out = self._layer(z, coefs, "fc3", False, False, torch.float32)
+        if mark:
+            mark("fc")
+            mark.flush()
+        return out
 
     def _coalition_models(self, coalitions: list[tuple]) -> torch.Tensor:
         # rows are padded to 256 bytes: the reduce kernel uses 128-bit accesses
@@ -136,6 +178,16 @@ class _LeNet5BatchEvaluator:
 
     @torch.no_grad()
     def __call__(self, coalitions: list[tuple]) -> list[float]:
+        import time
+
+        start = time.perf_counter()
+        try:
+            return self._evaluate(coalitions)
+        finally:  # every chunk ends with a device->host read, so host time covers the device work
+            STATS["calls"] += 1
+            STATS["seconds"] += time.perf_counter() - start
+
+    def _evaluate(self, coalitions: list[tuple]) -> list[float]:
         from . import gemm
 
         results: list[float] = []
@@ -149,9 +201,8 @@ class _LeNet5BatchEvaluator:
             acc = torch.zeros(S, 3, dtype=torch.float64, device=self.device)
             if self.fused:
                 coefs = self._coefficients(chunk)
-                for batch in tester._loader(phase):
-                    x, y = batch.inputs[0], batch.targets
-                    logits = self._forward_fused(x, coefs)
+                for key, x, y in self._test_slices(tester, phase):
+                    logits = self._forward_fused(x, coefs, key)
                     self._accumulate(acc, logits, y)
                 self._finish(tester, acc, results)
                 continue
@@ -198,6 +249,25 @@ class _LeNet5BatchEvaluator:
                 self._accumulate(acc, logits, y)
             self._finish(tester, acc, results)
         return results
+
+    def _test_slices(self, tester: Any, phase: Any) -> Any:
+        """The tester's evaluation set in slices of ``subset_eval_batch`` samples (device resident;
+        first-layer patches are cached per slice for the lifetime of this evaluator = one round)."""
+        from ..engine.dataloader import SampleLoader
+
+        loader = tester._loader(phase)
+        if not isinstance(loader, SampleLoader) or loader.shuffle:
+            for batch in loader:
+                yield None, batch.inputs[0], batch.targets
+            return
+        cached = self._patch_cache.get("slices")
+        if cached is None:
+            x, y, order = loader.epoch_tensors()
+            xs, ys = x.index_select(0, order), y.index_select(0, order)
+            cached = [(("patches", i), xs[i: i + self.eval_batch], ys[i: i + self.eval_batch])
+                      for i in range(0, ys.shape[0], self.eval_batch)]
+            self._patch_cache["slices"] = cached
+        yield from cached
 
     @staticmethod
     def _accumulate(acc: torch.Tensor, logits: torch.Tensor, y: torch.Tensor) -> None:

@@ -171,6 +171,12 @@ int dls_subset_gemm_bf16(const void* a, int a_shared, const float* const* worker
                          int stacked, void* c, int out_dtype, int m, int k_a, int k_w, int relu, int ptrs_aligned,
                          void* stream);
 
+/* Grouped im2col for the coalition evaluator: x [B][H][W][groups*channels] (channels-last), valid k x k
+ * windows -> cols [groups][B*OH*OW][k_pad], column order (kh, kw, c) when channels_last_k else (c, kh, kw),
+ * zero beyond channels*k*k.  elem_bytes 2 (bf16/fp16) or 4. */
+int dls_im2col_grouped(const void* x, int elem_bytes, int batch, int height, int width, int groups, int channels,
+                       int k, int k_pad, int channels_last_k, void* cols, void* stream);
+
 /* ---- graph family: fed_gnn / fed_gcn / fed_aas (reference: worker/graph_worker.py:205-216,
  *      252-269, 271-321) ------------------------------------------------------ */
 /* Ordered (stable) compaction of index pairs.  Pair i is kept iff mask[m(a[i])] && (b == NULL ||

@@ -349,3 +349,16 @@ def test_fused_bn_act_matches_pytorch(dev, dtype, shape, relu, with_res):
     torch.testing.assert_close(got[3], bn.bias.grad, **gtol)
     if with_res:
         torch.testing.assert_close(got[4].float(), r2.grad, **tol)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("groups,channels,k,channels_last_k", [(5, 6, 5, True), (3, 6, 5, False), (4, 3, 3, True),
+                                                               (1, 1, 5, False)])
+def test_im2col_grouped_matches_unfold(dev, dtype, groups, channels, k, channels_last_k):
+    from distributed_learning_simulator_b200.ops import misc as M
+
+    x = torch.randn(7, 14, 14, groups * channels, device=dev).to(dtype)
+    got = M.im2col_grouped(x, groups, k, channels_last_k)
+    ref = M.oracle_im2col_grouped(x, groups, k, channels_last_k, got.shape[-1])
+    assert got.shape == ref.shape and got.shape[-1] % 8 == 0
+    assert torch.equal(got, ref)

@@ -51,6 +51,9 @@ if __name__ == "__main__":
 
 def run(arm: str, conf: dict, rounds: int, work: str) -> float:
     conf = dict(conf, round=rounds)
+    extra = os.environ.get("ALGORITHM_KWARGS")  # JSON merged into algorithm_kwargs (A/B runs of our arm)
+    if extra and arm == "ours":
+        conf["algorithm_kwargs"] = dict(conf.get("algorithm_kwargs", {}), **json.loads(extra))
     script = os.path.join(work, f"{arm}_{rounds}.py")
     env = dict(os.environ, DLS_OUTPUT_ROOT=work, REF_LOG_LEVEL="WARNING", REF_GPUS="1")
     if arm == "ours":
