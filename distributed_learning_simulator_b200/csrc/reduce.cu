@@ -45,6 +45,17 @@ __device__ __forceinline__ void barrier_wait(uint32_t* const* peer_flags, int n_
     }
 }
 
+// NVLS: one store to a multicast address lands in the same offset of every GPU bound to the multicast
+// object (the NVSwitch replicates it), so the broadcast costs one NVLink write instead of one per peer.
+__device__ __forceinline__ void multimem_st_f4(float* mc, float4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z),
+                 "f"(v.w)
+                 : "memory");
+}
+__device__ __forceinline__ void multimem_st_f1(float* mc, float v) {
+    asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(mc), "f"(v) : "memory");
+}
+
 constexpr int kReduceThreads = 256;
 constexpr int kMaxDsts = 8;
 
@@ -54,7 +65,7 @@ template <bool kPeer>
 __global__ void __launch_bounds__(kReduceThreads, 2)
 fedavg_reduce_f32_kernel(const float* const* __restrict__ rows, const float* __restrict__ weights, int n_rows,
                          const float* __restrict__ old, float old_scale, double inv_total, DstTable dsts,
-                         int n_dsts, long long lo, long long hi, uint32_t* const* peer_flags, int n_ranks, int rank,
+                         int n_dsts, float* __restrict__ mc_dst, long long lo, long long hi, uint32_t* const* peer_flags, int n_ranks, int rank,
                          uint32_t epoch, uint32_t* __restrict__ nan_flag, unsigned int* done_counter) {
     extern __shared__ unsigned char smem_raw[];
     const float** s_rows = reinterpret_cast<const float**>(smem_raw);
@@ -105,9 +116,13 @@ fedavg_reduce_f32_kernel(const float* const* __restrict__ rows, const float* __r
                 r.z = (float)((double)old_scale * o.z + acc[u][2] * inv_total);
                 r.w = (float)((double)old_scale * o.w + acc[u][3] * inv_total);
                 saw_nan |= (r.x != r.x) | (r.y != r.y) | (r.z != r.z) | (r.w != r.w);
+                if (kPeer && mc_dst != nullptr) {
+                    multimem_st_f4(mc_dst + i, r);
+                } else {
 #pragma unroll
-                for (int d = 0; d < kMaxDsts; ++d)
-                    if (d < n_dsts) st_stream_f4(dsts.p[d] + i, r);
+                    for (int d = 0; d < kMaxDsts; ++d)
+                        if (d < n_dsts) st_stream_f4(dsts.p[d] + i, r);
+                }
             }
         }
     }
@@ -139,9 +154,13 @@ fedavg_reduce_f32_kernel(const float* const* __restrict__ rows, const float* __r
         r.z = (float)((double)old_scale * o.z + a2 * inv_total);
         r.w = (float)((double)old_scale * o.w + a3 * inv_total);
         saw_nan |= (r.x != r.x) | (r.y != r.y) | (r.z != r.z) | (r.w != r.w);
+        if (kPeer && mc_dst != nullptr) {
+            multimem_st_f4(mc_dst + i, r);
+        } else {
 #pragma unroll
-        for (int d = 0; d < kMaxDsts; ++d)
-            if (d < n_dsts) st_stream_f4(dsts.p[d] + i, r);
+            for (int d = 0; d < kMaxDsts; ++d)
+                if (d < n_dsts) st_stream_f4(dsts.p[d] + i, r);
+        }
     }
     // scalar tail (at most 3 elements, only in the slice that ends at P)
     for (long long i = lo + (n_vec << 2) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
@@ -149,7 +168,9 @@ fedavg_reduce_f32_kernel(const float* const* __restrict__ rows, const float* __r
         for (int k = 0; k < n_rows; ++k) a += (double)s_w[k] * s_rows[k][i];
         float r = (float)((double)old_scale * (old ? old[i] : 0.f) + a * inv_total);
         saw_nan |= (r != r);
-        for (int d = 0; d < n_dsts; ++d) dsts.p[d][i] = r;
+        if (kPeer && mc_dst != nullptr) multimem_st_f1(mc_dst + i, r);
+        else
+            for (int d = 0; d < n_dsts; ++d) dsts.p[d][i] = r;
     }
     if (__syncthreads_or(saw_nan) && threadIdx.x == 0) atomicOr(nan_flag, 1u);
 
@@ -288,10 +309,10 @@ extern "C" void dls_reset_launch_count(void) { g_launch_count.store(0); }
 
 static unsigned int* g_done_counter[16] = {nullptr};
 
-extern "C" int dls_fedavg_reduce_f32(const float* const* rows, const float* weights, int n_rows, const float* old,
-                                     float old_scale, double inv_total, float* const* dsts, int n_dsts,
-                                     long long lo, long long hi, uint32_t* const* peer_flags, int n_ranks, int rank,
-                                     uint32_t epoch, uint32_t* nan_flag, void* stream) {
+static int fedavg_reduce_f32_impl(const float* const* rows, const float* weights, int n_rows, const float* old,
+                                  float old_scale, double inv_total, float* const* dsts, int n_dsts, float* mc_dst,
+                                  long long lo, long long hi, uint32_t* const* peer_flags, int n_ranks, int rank,
+                                  uint32_t epoch, uint32_t* nan_flag, void* stream) {
     if (n_dsts < 1 || n_dsts > kMaxDsts) return fail_msg("dls_fedavg_reduce_f32: n_dsts must be in [1, 8]");
     if (n_rows < 1 || n_rows > 4096) return fail_msg("dls_fedavg_reduce_f32: n_rows must be in [1, 4096]");
     if (hi < lo || (lo & 3)) return fail_msg("dls_fedavg_reduce_f32: bad [lo, hi) (lo must be 4-aligned)");
@@ -316,15 +337,57 @@ extern "C" int dls_fedavg_reduce_f32(const float* const* rows, const float* weig
         if (per_sm < 1) return fail_msg("dls_fedavg_reduce_f32: kernel does not fit on an SM");
         const int grid = grid_for(n_vec, kReduceThreads, per_sm > 2 ? 2 : per_sm);
         fedavg_reduce_f32_kernel<true><<<grid, kReduceThreads, smem, s>>>(
-            rows, weights, n_rows, old, old_scale, inv_total, table, n_dsts, lo, hi, peer_flags, n_ranks, rank, epoch,
-            nan_flag, g_done_counter[dev]);
+            rows, weights, n_rows, old, old_scale, inv_total, table, n_dsts, mc_dst, lo, hi, peer_flags, n_ranks, rank,
+            epoch, nan_flag, g_done_counter[dev]);
     } else {
         const int grid = grid_for(n_vec, kReduceThreads, 4);
         fedavg_reduce_f32_kernel<false><<<grid, kReduceThreads, smem, s>>>(
-            rows, weights, n_rows, old, old_scale, inv_total, table, n_dsts, lo, hi, nullptr, 1, 0, 0, nan_flag,
+            rows, weights, n_rows, old, old_scale, inv_total, table, n_dsts, nullptr, lo, hi, nullptr, 1, 0, 0, nan_flag,
             nullptr);
     }
     DLS_LAUNCHED("fedavg_reduce_f32_kernel");
+    return 0;
+}
+
+extern "C" int dls_fedavg_reduce_f32(const float* const* rows, const float* weights, int n_rows, const float* old,
+                                     float old_scale, double inv_total, float* const* dsts, int n_dsts,
+                                     long long lo, long long hi, uint32_t* const* peer_flags, int n_ranks, int rank,
+                                     uint32_t epoch, uint32_t* nan_flag, void* stream) {
+    return fedavg_reduce_f32_impl(rows, weights, n_rows, old, old_scale, inv_total, dsts, n_dsts, nullptr, lo, hi,
+                                  peer_flags, n_ranks, rank, epoch, nan_flag, stream);
+}
+
+extern "C" int dls_fedavg_reduce_f32_mc(const float* const* rows, const float* weights, int n_rows, const float* old,
+                                        float old_scale, double inv_total, float* mc_dst, long long lo, long long hi,
+                                        uint32_t* const* peer_flags, int n_ranks, int rank, uint32_t epoch,
+                                        uint32_t* nan_flag, void* stream) {
+    if (mc_dst == nullptr || peer_flags == nullptr || n_ranks < 2)
+        return fail_msg("dls_fedavg_reduce_f32_mc: needs a multicast destination and the peers' flag blocks");
+    if ((uintptr_t)mc_dst & 15) return fail_msg("dls_fedavg_reduce_f32_mc: destination must be 16-byte aligned");
+    float* none[1] = {mc_dst};  // the table is unused on the multicast path; keep n_dsts valid
+    return fedavg_reduce_f32_impl(rows, weights, n_rows, old, old_scale, inv_total, none, 1, mc_dst, lo, hi, peer_flags,
+                                  n_ranks, rank, epoch, nan_flag, stream);
+}
+
+// K9 on its own: copy n floats from src to the same offset of every GPU bound to the multicast address
+namespace dls {
+__global__ void __launch_bounds__(256)
+multimem_bcast_kernel(const float* __restrict__ src, float* __restrict__ mc_dst, long long n) {
+    const long long n_vec = n >> 2;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < n_vec; v += stride)
+        multimem_st_f4(mc_dst + (v << 2), ld_stream_f4(src + (v << 2)));
+    for (long long i = (n_vec << 2) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+        multimem_st_f1(mc_dst + i, src[i]);
+    __threadfence_system();
+}
+}  // namespace dls
+
+extern "C" int dls_multimem_bcast_f32(const float* src, float* mc_dst, long long n, void* stream) {
+    if (n < 1 || mc_dst == nullptr) return fail_msg("dls_multimem_bcast_f32: empty");
+    if (((uintptr_t)src | (uintptr_t)mc_dst) & 15) return fail_msg("dls_multimem_bcast_f32: 16-byte alignment");
+    multimem_bcast_kernel<<<grid_for((n >> 2) + 1, 256, 4), 256, 0, (cudaStream_t)stream>>>(src, mc_dst, n);
+    DLS_LAUNCHED("multimem_bcast_kernel");
     return 0;
 }
 

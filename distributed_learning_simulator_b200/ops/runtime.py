@@ -28,6 +28,9 @@ class DlsPackedRow(ctypes.Structure):
 _SIGNATURES = {
     "dls_fedavg_reduce_f32": [c_void_p, c_void_p, c_int, c_void_p, c_float, c_double, c_void_p, c_int, c_ll, c_ll,
                               c_void_p, c_int, c_int, c_u32, c_void_p, c_void_p],
+    "dls_fedavg_reduce_f32_mc": [c_void_p, c_void_p, c_int, c_void_p, c_float, c_double, c_void_p, c_ll, c_ll,
+                                 c_void_p, c_int, c_int, c_u32, c_void_p, c_void_p],
+    "dls_multimem_bcast_f32": [c_void_p, c_void_p, c_ll, c_void_p],
     "dls_fedavg_reduce_packed": [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p,
                                  c_void_p],
     "dls_sgd_step": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_float, c_float,

@@ -87,6 +87,38 @@ class SymmetricBuffer:
         return self.ptrs[rank] + byte_offset
 
 
+class MulticastBuffer:
+    """Same contract as ``SymmetricBuffer`` plus ``mc_ptr``: one virtual address whose stores the
+    NVSwitch replicates into every rank's copy (NVLS).  Allocation, handle exchange and the multicast
+    binding are PyTorch's symmetric-memory plumbing; the kernels that write through ``mc_ptr`` are
+    ours (csrc/reduce.cu: ``multimem.st``).  Raises when the platform has no multicast support."""
+
+    def __init__(self, ctx: "DistributedContext", nbytes: int) -> None:
+        import torch.distributed._symmetric_memory as symm_mem
+
+        self.nbytes = int(nbytes)
+        self.ctx = ctx
+        self._tensor = symm_mem.empty(self.nbytes, dtype=torch.uint8, device=ctx.device)
+        self._tensor.zero_()
+        self._handle = symm_mem.rendezvous(self._tensor, dist.group.WORLD)
+        self.mc_ptr = int(getattr(self._handle, "multicast_ptr", 0) or 0)
+        if not self.mc_ptr:
+            raise RuntimeError("symmetric memory has no multicast address on this platform")
+        self.ptrs = [int(p) for p in self._handle.buffer_ptrs]
+        self.local_ptr = self.ptrs[ctx.rank]
+        assert self.local_ptr == self._tensor.data_ptr()
+        torch.cuda.synchronize(ctx.device)
+        dist.barrier(group=ctx.control)
+
+    def local_tensor(self, dtype: torch.dtype, numel: int, byte_offset: int = 0) -> torch.Tensor:
+        itemsize = torch.empty(0, dtype=dtype).element_size()
+        assert byte_offset + numel * itemsize <= self.nbytes and byte_offset % itemsize == 0
+        return self._tensor[byte_offset: byte_offset + numel * itemsize].view(dtype)
+
+    def ptr(self, rank: int, byte_offset: int = 0) -> int:
+        return self.ptrs[rank] + byte_offset
+
+
 class ArenaPayload(dict):
     """Message payload that lives in a rank's upload arena.  ``ptr`` is valid in THIS
     process (local or peer-mapped); ``local`` is a tensor view when the row is ours."""
@@ -131,6 +163,8 @@ class DistributedContext:
         self.peer_reads_pending = False
         self._flag_table: torch.Tensor | None = None
         self.p2p_reductions = 0
+        self.multicast = False
+        self.multicast_reductions = 0
         self._table_cache: dict = {}
         get_logger().debug("rank %s/%s on %s, p2p=%s", self.rank, self.world, self.device, self.use_p2p)
 
@@ -155,11 +189,27 @@ class DistributedContext:
         self.slots = -(-worker_number // self.world)
         self.row_bytes = ((layout.total * 4 + 255) // 256) * 256
         self.arena = SymmetricBuffer(self, self.row_bytes * self.slots)
-        self.globals = SymmetricBuffer(self, self.row_bytes * 2)
+        self.globals = self._global_buffers(self.row_bytes * 2)
         self.flags = SymmetricBuffer(self, 256)
         self._flag_table = runtime.pointer_table(self.flags.ptrs, self.device)
         self._nan = torch.zeros(1, dtype=torch.int32, device=self.device)
         self.epoch = 0
+
+    def _global_buffers(self, nbytes: int) -> Any:
+        """The two global-model buffers: multicast-bound when NVLS is available on every rank
+        (``DLS_NVLS=0`` forces the per-peer store path), plain IPC-mapped otherwise."""
+        buf: Any = None
+        if os.environ.get("DLS_NVLS", "1") != "0":
+            try:
+                buf = MulticastBuffer(self, nbytes)
+            except Exception as e:  # noqa: BLE001 - no NVSwitch / no fabric handles / old driver
+                get_logger().info("NVLS multicast unavailable on rank %d: %s", self.rank, e)
+                buf = None
+        everyone = all(self.exchange(buf is not None))
+        if buf is not None and not everyone:
+            buf = None
+        self.multicast = buf is not None
+        return buf if buf is not None else SymmetricBuffer(self, nbytes)
 
     def arena_row(self, slot: int) -> torch.Tensor:
         assert self.arena is not None and self.layout is not None
@@ -197,12 +247,20 @@ class DistributedContext:
                       torch.tensor(weights, dtype=torch.float32).pin_memory().to(self.device, non_blocking=True))
             self._table_cache[key] = cached
         rows, w = cached
-        dsts = (ctypes.c_void_p * self.world)(*[self.globals.ptr(r, off) for r in range(self.world)])
         self.epoch += 1
         self._nan.zero_()
-        runtime.call("dls_fedavg_reduce_f32", rows.data_ptr(), w.data_ptr(), len(payloads), runtime.ptr(old),
-                     float(old_scale), float(inv_total), dsts, self.world, lo, hi, self._flag_table.data_ptr(),
-                     self.world, self.rank, self.epoch, self._nan.data_ptr(), runtime.stream_ptr(self.device))
+        if self.multicast:
+            # NVLS: each output vector is one multimem.st that the switch replicates into every rank's buffer
+            runtime.call("dls_fedavg_reduce_f32_mc", rows.data_ptr(), w.data_ptr(), len(payloads), runtime.ptr(old),
+                         float(old_scale), float(inv_total), self.globals.mc_ptr + off, lo, hi,
+                         self._flag_table.data_ptr(), self.world, self.rank, self.epoch, self._nan.data_ptr(),
+                         runtime.stream_ptr(self.device))
+            self.multicast_reductions += 1
+        else:
+            dsts = (ctypes.c_void_p * self.world)(*[self.globals.ptr(r, off) for r in range(self.world)])
+            runtime.call("dls_fedavg_reduce_f32", rows.data_ptr(), w.data_ptr(), len(payloads), runtime.ptr(old),
+                         float(old_scale), float(inv_total), dsts, self.world, lo, hi, self._flag_table.data_ptr(),
+                         self.world, self.rank, self.epoch, self._nan.data_ptr(), runtime.stream_ptr(self.device))
         self.p2p_reductions += 1
         verdict = self.flags.local_tensor(torch.int32, 32)[16:25].cpu().tolist()
         if verdict[8]:

@@ -28,6 +28,15 @@ int dls_fedavg_reduce_f32(const float* const* rows, const float* weights, int n_
                           float old_scale, double inv_total, float* const* dsts, int n_dsts, long long lo,
                           long long hi, uint32_t* const* peer_flags, int n_ranks, int rank, uint32_t epoch,
                           uint32_t* nan_flag, void* stream);
+/* Same reduction, broadcast through NVLS: every output vector is ONE multimem.st to `mc_dst`, the
+ * multicast address of the destination (NVSwitch replicates it into every bound GPU, the caller's
+ * included), instead of one peer store per destination.  Needs the flag barriers (n_ranks >= 2). */
+int dls_fedavg_reduce_f32_mc(const float* const* rows, const float* weights, int n_rows, const float* old,
+                             float old_scale, double inv_total, float* mc_dst, long long lo, long long hi,
+                             uint32_t* const* peer_flags, int n_ranks, int rank, uint32_t epoch, uint32_t* nan_flag,
+                             void* stream);
+/* Global-model broadcast on its own: n floats from src to every GPU behind mc_dst. */
+int dls_multimem_bcast_f32(const float* src, float* mc_dst, long long n, void* stream);
 
 /* Same reduction with per-row decode at load time: kind 0 fp32, 1 stochastic-255 packed
  * (u8 magnitudes + sign plane + per-tensor scale), 2 NNADQ packed (per-tensor bit width);

@@ -48,8 +48,20 @@ for rnd in range(3):
         ref = ref + r.double() * (wt / sum(weights))
     errs.append(float((out.double() - ref).abs().max()))
     old = out.clone()
+bcast_err = None
+if ctx.multicast:
+    # K9 on its own: rank 0 stores through the multicast address, every rank finds the data in its buffer
+    from distributed_learning_simulator_b200.ops import runtime
+    ctx.fence()
+    src = torch.arange(n, device=ctx.device, dtype=torch.float32) * 0.5 + 3.0
+    if ctx.rank == 0:
+        runtime.call("dls_multimem_bcast_f32", src.data_ptr(), ctx.globals.mc_ptr, n, runtime.stream_ptr(ctx.device))
+    ctx.fence()
+    bcast_err = float((ctx.globals.local_tensor(torch.float32, n) - src).abs().max())
+    ctx.fence()
 with open(os.path.join({out!r}, "p2p_%d.json" % ctx.rank), "w") as f:
-    json.dump({{"errs": errs, "reductions": ctx.p2p_reductions}}, f)
+    json.dump({{"errs": errs, "reductions": ctx.p2p_reductions, "multicast": ctx.multicast,
+               "multicast_reductions": ctx.multicast_reductions, "bcast_err": bcast_err}}, f)
 
 from distributed_learning_simulator_b200 import load_config_from_dict, train
 from distributed_learning_simulator_b200.training import get_last_training_result
@@ -73,11 +85,14 @@ def _free_port() -> int:
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
-def test_p2p_reduce_and_distributed_training(tmp_path):
+@pytest.mark.parametrize("nvls", ["1", "0"])
+def test_p2p_reduce_and_distributed_training(tmp_path, nvls):
+    """nvls=1: the broadcast half of the fused kernel is one multimem.st per vector (NVSwitch multicast)
+    when the platform offers it; nvls=0: one peer store per destination.  Same results either way."""
     world = 2
     script = tmp_path / "run.py"
     script.write_text(SCRIPT.format(root=ROOT, out=str(tmp_path)))
-    env = dict(os.environ, DLS_OUTPUT_ROOT=str(tmp_path))
+    env = dict(os.environ, DLS_OUTPUT_ROOT=str(tmp_path), DLS_NVLS=nvls)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), str(script)]
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
@@ -86,6 +101,11 @@ def test_p2p_reduce_and_distributed_training(tmp_path):
         p2p = json.load(open(tmp_path / f"p2p_{r}.json"))
         assert max(p2p["errs"]) < 1e-5, p2p
         assert p2p["reductions"] == 3
+        if nvls == "0":
+            assert not p2p["multicast"] and p2p["multicast_reductions"] == 0
+        elif p2p["multicast"]:
+            assert p2p["multicast_reductions"] == 3 and p2p["bcast_err"] == 0.0
+        print("multicast available:", p2p["multicast"])
     t0, t1 = (json.load(open(tmp_path / f"train_{r}.json")) for r in range(world))
     assert t0["performance"] == t1["performance"]
     assert t0["p2p_reductions"] == 3 and t1["p2p_reductions"] == 3
