@@ -164,6 +164,7 @@ class DistributedContext:
         self._flag_table: torch.Tensor | None = None
         self.p2p_reductions = 0
         self.multicast = False
+        self.multicast_reduce = False
         self.multicast_reductions = 0
         self._table_cache: dict = {}
         get_logger().debug("rank %s/%s on %s, p2p=%s", self.rank, self.world, self.device, self.use_p2p)
@@ -209,6 +210,12 @@ class DistributedContext:
         if buf is not None and not everyone:
             buf = None
         self.multicast = buf is not None
+        # Measured (profiles/agg_sweep.md): in the all-to-all pattern of the fused reduce every GPU's NVLink
+        # INGRESS carries the peers' rows plus the peers' slices either way, and a multicast store also sends
+        # the writer's own slice back through the switch, so per-destination peer stores are the faster
+        # broadcast half there; the multicast store wins for one-to-all broadcasts (dls_multimem_bcast_f32).
+        # DLS_NVLS_REDUCE=1 selects the multimem.st epilogue in the fused kernel as well.
+        self.multicast_reduce = self.multicast and os.environ.get("DLS_NVLS_REDUCE", "0") == "1"
         return buf if buf is not None else SymmetricBuffer(self, nbytes)
 
     def arena_row(self, slot: int) -> torch.Tensor:
@@ -249,7 +256,7 @@ class DistributedContext:
         rows, w = cached
         self.epoch += 1
         self._nan.zero_()
-        if self.multicast:
+        if self.multicast_reduce:
             # NVLS: each output vector is one multimem.st that the switch replicates into every rank's buffer
             runtime.call("dls_fedavg_reduce_f32_mc", rows.data_ptr(), w.data_ptr(), len(payloads), runtime.ptr(old),
                          float(old_scale), float(inv_total), self.globals.mc_ptr + off, lo, hi,

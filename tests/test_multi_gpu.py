@@ -92,7 +92,7 @@ def test_p2p_reduce_and_distributed_training(tmp_path, nvls):
     world = 2
     script = tmp_path / "run.py"
     script.write_text(SCRIPT.format(root=ROOT, out=str(tmp_path)))
-    env = dict(os.environ, DLS_OUTPUT_ROOT=str(tmp_path), DLS_NVLS=nvls)
+    env = dict(os.environ, DLS_OUTPUT_ROOT=str(tmp_path), DLS_NVLS=nvls, DLS_NVLS_REDUCE=nvls)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), str(script)]
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)

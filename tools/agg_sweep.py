@@ -5,8 +5,12 @@ pre-weighted vectors (the baseline variant).  Launch with torch.distributed.run,
 
 Timing: CUDA events on the launching stream, 3 warm-up + 10 timed iterations, max over ranks.
 algbw = bytes of one vector / time; busbw = algbw * 2 (G-1)/G, the usual all-reduce convention.
-Roofline of the fused kernel: every rank loads (G-1)/G of the vector from peers and stores
-(G-1)/G of it to peers, so time >= (G-1)/G * bytes / (link bandwidth per direction)."""
+Roofline of the fused kernel, per GPU and per NVLink direction: INGRESS = the peers' rows of my slice
+arriving for my loads ((G-1)/G of a vector) + the other ranks' reduced slices arriving in my
+global-model buffer ((G-1)/G of a vector) = 2 (G-1)/G * bytes; EGRESS is the mirror image with peer
+stores (2 (G-1)/G * bytes) and drops to bytes with the NVLS multicast store (my slice leaves once, the
+switch replicates it), so the bound is the ingress: time >= 2 (G-1)/G * bytes / (link bandwidth per
+direction).  (An earlier version of this tool counted only one of the two ingress streams.)"""
 import json
 import os
 import sys
@@ -67,14 +71,24 @@ def main():
             dist.all_reduce(buf)
             buf.add_(old)
 
-        ms_f, ms_n = timed(fused), timed(nccl)
+        # the broadcast half through NVSwitch multicast (one multimem.st per vector) when the platform has
+        # it, and through one peer store per destination; the multicast-bound buffers serve both
+        has_mc = ctx.multicast
+        ctx.multicast_reduce = False
+        ms_f = timed(fused)          # default: one peer store per destination
+        ms_mc = None
+        if has_mc:
+            ctx.multicast_reduce = True
+            ms_mc = timed(fused)     # broadcast half as multimem.st
+            ctx.multicast_reduce = False
+        ms_n = timed(nccl)
         out = ctx.p2p_reduce(payloads, weights, old, 1.0, inv).flat
         ref = pre.clone()
         dist.all_reduce(ref)
         err = float((out - ref).abs().max())
         bytes_ = n * 4
-        roof_ms = (G - 1) / G * bytes_ / (LINK_GBS * 1e9) * 1e3
-        rows.append({"MB": mb, "fused_ms": ms_f, "nccl_ms": ms_n, "fused_algbw_GBs": bytes_ / ms_f / 1e6,
+        roof_ms = 2 * (G - 1) / G * bytes_ / (LINK_GBS * 1e9) * 1e3
+        rows.append({"MB": mb, "fused_ms": ms_f, "fused_multimem_store_ms": ms_mc, "nccl_ms": ms_n, "fused_algbw_GBs": bytes_ / ms_f / 1e6,
                      "nccl_algbw_GBs": bytes_ / ms_n / 1e6, "fused_busbw_GBs": bytes_ / ms_f / 1e6 * 2 * (G - 1) / G,
                      "roofline_ms": roof_ms, "fused_fraction_of_roofline": roof_ms / ms_f, "max_abs_err": err})
         if ctx.rank == 0:
