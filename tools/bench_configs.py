@@ -31,10 +31,18 @@ CONFIGS = {
 }
 
 OURS = r"""
-import sys, json
+import sys, json, time
 sys.path.insert(0, {root!r})
+import torch
 from distributed_learning_simulator_b200 import load_config_from_dict, train
+from distributed_learning_simulator_b200.utils.observer import add_round_observer
+stamps = []
+def stamp(server, round_number):
+    torch.cuda.synchronize()
+    stamps.append(time.perf_counter())
+add_round_observer(stamp)
 train(load_config_from_dict({conf!r}))
+print("ROUND_STAMPS " + json.dumps(stamps))
 """
 
 REFERENCE = r"""
@@ -70,7 +78,13 @@ def run(arm: str, conf: dict, rounds: int, work: str) -> float:
                          timeout=int(os.environ.get("ARM_TIMEOUT", "900")))
     if res.returncode != 0:
         raise RuntimeError((res.stderr or res.stdout)[-600:])
+    for line in res.stdout.splitlines():
+        if line.startswith("ROUND_STAMPS "):
+            ROUND_STAMPS[(arm, rounds)] = json.loads(line.split(" ", 1)[1])
     return time.time() - start
+
+
+ROUND_STAMPS: dict = {}
 
 
 def main() -> None:
@@ -87,6 +101,13 @@ def main() -> None:
                 out[name][arm] = {"wall_s": {r1: round(t1, 2), r2: round(t2, 2)},
                                   "s_per_round": round((t2 - t1) / (r2 - r1), 3),
                                   "rounds_per_s": round((r2 - r1) / max(t2 - t1, 1e-9), 4)}
+                stamps = ROUND_STAMPS.get((arm, r2))
+                if stamps and len(stamps) >= 2:
+                    # our arm also reports the server's own round-end clock (after a device synchronize):
+                    # rounds 2..R2 of the long run, free of start-up noise
+                    deltas = [b - a for a, b in zip(stamps, stamps[1:])]
+                    out[name][arm]["round_seconds"] = [round(d, 4) for d in deltas]
+                    out[name][arm]["s_per_round_in_process"] = round(sum(deltas) / len(deltas), 4)
             except Exception as e:  # noqa: BLE001
                 out[name][arm] = {"error": str(e)[-400:]}
             print(name, arm, json.dumps(out[name][arm]), flush=True)
