@@ -19,6 +19,7 @@ from typing import Any
 
 import torch
 
+from ..ops import conv as conv_ops
 from ..ops import runtime
 from ..ops import sgd as sgd_ops
 from .dataloader import SampleLoader
@@ -73,6 +74,10 @@ class GraphTrainStep:
         self.shadow_flags: torch.Tensor | None = None
         if self.use_shadow:
             self.shadow_flags = torch.tensor(self.util.shadow_flags(), dtype=torch.uint8, device=self.device)
+        # weight-gradient kernels run on a side stream: a parallel branch of the captured graph (ops/conv.py)
+        self.side_stream: torch.cuda.Stream | None = None
+        if os.environ.get("DLS_SPLIT_BACKWARD", "1") != "0" and conv_ops.install(trainer.model) > 0:
+            self.side_stream = torch.cuda.Stream(device=self.device)
         # state: [0] lr/optimizer step, [1] momentum initialised, [2] batch index in epoch
         self.state = torch.zeros(4, dtype=torch.int32, device=self.device)
         self.acc = torch.zeros(3, dtype=torch.float64, device=self.device)
@@ -104,10 +109,12 @@ class GraphTrainStep:
         hp = t.hyper_parameter
         sgd_ops.gather_batch(x_all, y_all, self.order, n_order, self.state, 2, step.x, step.y,
                              batch_stride=hp.batch_size)
-        with t._autocast():
+        with t._autocast(), conv_ops.split_backward(self.side_stream):
             output = t.model(step.x)
             loss = t.loss_fun(output.float(), step.y)
         loss.backward()
+        if self.side_stream is not None:
+            torch.cuda.current_stream(self.device).wait_stream(self.side_stream)  # join before the optimizer
         if step.grad_table is None:
             step.grad_table = torch.zeros(self.n_tensors, dtype=torch.int64, device=self.device)
         sgd_ops.sgd_step(self.flat, self.momentum_buf if hp.momentum else None, step.grad_table, self.offsets,

@@ -58,9 +58,15 @@ def summary(reset: bool = True) -> dict:
         else:
             end.synchronize()
             ms = start.elapsed_time(end)
-        entry = out.setdefault(name, {"count": 0, "total_ms": 0.0})
+        entry = out.setdefault(name, {"count": 0, "total_ms": 0.0, "min_ms": float("inf"), "max_ms": 0.0,
+                                      "_all": []})
         entry["count"] += 1
         entry["total_ms"] += ms
+        entry["min_ms"] = min(entry["min_ms"], ms)
+        entry["max_ms"] = max(entry["max_ms"], ms)
+        entry["_all"].append(ms)
     for entry in out.values():
         entry["mean_ms"] = entry["total_ms"] / max(entry["count"], 1)
+        ordered = sorted(entry.pop("_all"))
+        entry["median_ms"] = ordered[len(ordered) // 2]  # first calls include lazy initialisation / graph capture
     return out

@@ -11,7 +11,7 @@ from distributed_learning_simulator_b200 import load_config_from_dict, train  # 
 
 if __name__ == "__main__":
     train(load_config_from_dict({
-        "dataset_name": "CIFAR10", "model_name": "resnet18", "distributed_algorithm": "fed_avg",
+        "dataset_name": "CIFAR10", "model_name": os.environ.get("MODEL", "resnet18"), "distributed_algorithm": "fed_avg",
         "optimizer_name": "SGD", "learning_rate_scheduler_name": "CosineAnnealingLR",
         "worker_number": int(os.environ.get("WORKERS", "2")), "batch_size": 64, "round": 2, "epoch": 1,
         "learning_rate": 0.1, "use_amp": True, "log_level": "WARNING",
