@@ -24,6 +24,26 @@ def test_linear_bf16(m, n, k, bias, relu):
     torch.testing.assert_close(out, ref, rtol=1e-3, atol=1e-3 * (k ** 0.5))
 
 
+@pytest.mark.parametrize("m,n,k,batch", [(1000, 300, 512, 1), (256, 128, 64, 1), (777, 1000, 264, 1), (513, 200, 136, 3),
+                                         (4096, 2048, 1024, 1)])
+@pytest.mark.parametrize("pair", ["1", "0"])
+def test_linear_bf16_cta_pair(m, n, k, batch, pair, monkeypatch):
+    """cta_group::2 variant (two CTAs on one 256 x N tile, leader-issued M = 256 MMAs) against the same
+    oracle, including ragged M / N tails and batches; pair=0 pins the single-CTA kernel on the same shapes."""
+    from distributed_learning_simulator_b200.ops import gemm as G
+
+    monkeypatch.setenv("DLS_GEMM_2CTA", pair)
+    dev = torch.device("cuda", 0)
+    g = torch.Generator(device="cuda").manual_seed(m + n + k)
+    x = torch.randn(batch, m, k, device=dev, generator=g).bfloat16()
+    w = (torch.randn(batch, n, k, device=dev, generator=g) * 0.1).bfloat16()
+    b = torch.randn(batch, n, device=dev, generator=g)
+    out = G.linear_bf16(x, w, b, relu=True, out_dtype=torch.float32)
+    torch.cuda.synchronize()
+    ref = G.oracle_linear(x, w, b, relu=True)
+    torch.testing.assert_close(out, ref, rtol=1e-3, atol=1e-3 * (k ** 0.5))
+
+
 def test_linear_bf16_batched_and_bf16_out():
     from distributed_learning_simulator_b200.ops import gemm as G
 
