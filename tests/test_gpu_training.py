@@ -118,3 +118,38 @@ def test_batched_coalition_evaluator_matches_sequential():
         for rnd in (0, 1, 2):
             assert abs(results[mode]["performance"][rnd]["test_accuracy"]
                        - results["sequential"]["performance"][rnd]["test_accuracy"]) < 0.02  # independent trainings
+
+
+def test_split_backward_convolution_matches_autograd():
+    """ops/conv.py: weight gradients computed on a side stream (joined by the caller) equal stock autograd,
+    with and without autocast, for strided / padded / bias-carrying channels-last convolutions."""
+    from distributed_learning_simulator_b200.ops import conv as C
+
+    dev = torch.device("cuda", 0)
+    side = torch.cuda.Stream(device=dev)
+    g = torch.Generator(device="cuda").manual_seed(0)
+    for amp, (cin, cout, k, stride, pad, bias) in [(False, (3, 16, 3, 1, 1, False)), (True, (16, 32, 3, 2, 1, False)),
+                                                   (True, (32, 64, 1, 2, 0, True)), (False, (8, 8, 5, 1, 0, True))]:
+        ref = torch.nn.Conv2d(cin, cout, k, stride=stride, padding=pad, bias=bias).to(dev).to(memory_format=torch.channels_last)
+        new = torch.nn.Conv2d(cin, cout, k, stride=stride, padding=pad, bias=bias).to(dev).to(memory_format=torch.channels_last)
+        new.load_state_dict(ref.state_dict())
+        assert C.install(new) == 1
+        x = torch.randn(8, cin, 16, 16, device=dev, generator=g).contiguous(memory_format=torch.channels_last)
+        xs = [x.clone().requires_grad_(True) for _ in range(2)]
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=amp):
+            y_ref = ref(xs[0])
+            with C.split_backward(side):
+                y_new = new(xs[1])
+        assert y_new.dtype == y_ref.dtype and torch.equal(y_new, y_ref)
+        w = torch.randn_like(y_ref)
+        (y_ref * w).sum().backward()
+        (y_new * w).sum().backward()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize()
+        assert torch.equal(xs[0].grad, xs[1].grad)
+        assert new.weight.grad.dtype == new.weight.dtype and torch.equal(ref.weight.grad, new.weight.grad)
+        if bias:
+            assert torch.equal(ref.bias.grad, new.bias.grad)
+    # outside a split_backward context the patched layer is the stock layer
+    y = new(xs[1].detach())
+    assert y.grad_fn is None or "SplitBackward" not in type(y.grad_fn).__name__
