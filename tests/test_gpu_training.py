@@ -121,7 +121,7 @@ def test_batched_coalition_evaluator_matches_sequential():
 
 
 def test_split_backward_convolution_matches_autograd():
-    """ops/conv.py: weight gradients computed on a side stream (joined by the caller) equal stock autograd,
+    """ops/conv.py: weight gradients computed on a side stream (joined by the caller) match stock autograd,
     with and without autocast, for strided / padded / bias-carrying channels-last convolutions."""
     from distributed_learning_simulator_b200.ops import conv as C
 
@@ -146,10 +146,14 @@ def test_split_backward_convolution_matches_autograd():
         (y_new * w).sum().backward()
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize()
-        assert torch.equal(xs[0].grad, xs[1].grad)
-        assert new.weight.grad.dtype == new.weight.dtype and torch.equal(ref.weight.grad, new.weight.grad)
+        # same ATen op, but asked for one gradient at a time: cuDNN may pick another algorithm, so compare
+        # to rounding rather than bit for bit
+        tol = dict(rtol=2e-2, atol=2e-1) if amp else dict(rtol=1e-2, atol=1e-1)  # fp32 convs may run as TF32
+        torch.testing.assert_close(xs[1].grad, xs[0].grad, **tol)
+        assert new.weight.grad.dtype == new.weight.dtype
+        torch.testing.assert_close(new.weight.grad, ref.weight.grad, **tol)
         if bias:
-            assert torch.equal(ref.bias.grad, new.bias.grad)
+            torch.testing.assert_close(new.bias.grad, ref.bias.grad, **tol)
     # outside a split_backward context the patched layer is the stock layer
     y = new(xs[1].detach())
     assert y.grad_fn is None or "SplitBackward" not in type(y.grad_fn).__name__
