@@ -20,7 +20,7 @@ import torch
 
 from ..engine.log import get_logger
 from ..engine.tensor import TensorDict
-from ..message import DeltaParameterMessage, Message, ParameterMessage
+from ..message import Message, ParameterMessage
 from .aggregation_algorithm import AggregationAlgorithm
 
 

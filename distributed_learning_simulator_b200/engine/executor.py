@@ -13,9 +13,8 @@ from .dataset import DatasetCollection
 from .device import capture_guard
 from .hook import HookCollection
 from .hyper_parameter import HyperParameter
-from .log import get_logger
 from .metric import PerformanceMetric
-from .ml_type import ExecutorHookPoint, MachineLearningPhase
+from .ml_type import MachineLearningPhase
 from .model_util import ModelUtil
 
 

@@ -24,7 +24,6 @@ from ..ops import runtime
 from ..ops import sgd as sgd_ops
 from .dataloader import SampleLoader
 from .device import capture_guard
-from .log import get_logger
 from .ml_type import ExecutorHookPoint, MachineLearningPhase
 
 

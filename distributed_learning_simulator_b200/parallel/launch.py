@@ -1,6 +1,5 @@
 """``train()`` under ``torch.distributed.run``: each rank runs its local workers and a
 server replica (see ``parallel/topology.py``)."""
-import os
 import threading
 from typing import Any
 

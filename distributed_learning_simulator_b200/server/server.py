@@ -8,7 +8,6 @@ until some pending worker has data instead of sweeping and sleeping one second
 (server.py:84-85; SURVEY.md defect D7), and a watchdog (``config.round_timeout``) turns a
 dead worker into an error instead of an endless wait.
 """
-import copy
 import functools
 import os
 import pickle

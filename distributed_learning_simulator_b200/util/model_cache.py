@@ -7,7 +7,6 @@ pulls every tensor to the CPU first (model_cache.py:24,34,42); here the cache st
 whatever device the model lives on -- with flat payloads ``get_parameter_diff`` is one
 subtraction over ``[P]`` in HBM and nothing crosses PCIe.
 """
-import torch
 
 from ..engine.storage import DataStorage
 from ..engine.tensor import TensorDict, tensor_to

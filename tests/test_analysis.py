@@ -1,7 +1,6 @@
 """Analysis tools against a real (tiny) run: log scraping, Session, graph analyzer, ModuleDiff."""
 import os
 
-import torch
 
 from distributed_learning_simulator_b200 import load_config_from_file, train
 from distributed_learning_simulator_b200.analysis import GraphSession, ModuleDiff, Session

@@ -2,7 +2,6 @@
 packed on one device (config 4), Transformer FedPAQ / sign_SGD on IMDB-shape tokens (config 5),
 and the end-to-end data path (pinned host shards copied every epoch)."""
 import pytest
-import torch
 
 pytestmark = pytest.mark.gpu
 

@@ -125,8 +125,6 @@ def test_fed_gnn_trains_through_the_graph_kernels(dev):
     """Embedding-sharing fed_gnn on the GPU: per-batch edge filtering, boundary gather, halo merge and
     the GCN aggregation all run as this library's kernels (launch counter), and the run reaches the
     accuracy of the same configuration forced onto the PyTorch oracles."""
-    import os
-
     from distributed_learning_simulator_b200 import load_config_from_file, train
     from distributed_learning_simulator_b200.ops import runtime
     from distributed_learning_simulator_b200.training import get_last_training_result
