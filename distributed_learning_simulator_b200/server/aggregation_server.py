@@ -79,6 +79,11 @@ class AggregationServer(Server):
                              self.config.round)
 
     def __write_checkpoint(self, parameter: TensorDict) -> None:
+        from ..parallel import context as parallel_context
+
+        ctx = parallel_context.current()
+        if ctx is not None and ctx.rank != 0:
+            return  # server replicas are identical: one writer is enough
         state = {"round": self._round_number, "stat": self.__stat, "plateau": self.__plateau,
                  "max_acc": self.__max_acc, "best_acc_saved": self.__best_acc_saved,
                  "parameter": dict(tensor_to(dict(parameter), device="cpu"))}
