@@ -29,6 +29,9 @@ class GTGShapleyValue(ShapleyValue):
                  speculative_prefetch: bool = True, **kwargs) -> None:
         super().__init__(players, last_round_metric, **kwargs)
         self.speculative_prefetch = speculative_prefetch
+        # every prefix of every surviving permutation is n^2 coalitions per sweep: worth it while a batched
+        # launch is cheaper than the cache misses it avoids, not for hundreds of players
+        self.speculative_max_players = 32
         self.eps = eps
         self.round_trunc_threshold = round_trunc_threshold
         self.converge_min = converge_min if converge_min is not None else max(30, self.player_number)
@@ -74,7 +77,7 @@ class GTGShapleyValue(ShapleyValue):
             # level-2 prefixes of the whole sweep are needed unless truncated at level 1: batch them
             self.prefetch([perm[:2] for perm in sweep
                            if abs(v_all - self.metric(perm[:1])) >= self.eps and n >= 2])
-            if self.batch_metric_fun is not None and self.speculative_prefetch:
+            if self.batch_metric_fun is not None and self.speculative_prefetch and n <= self.speculative_max_players:
                 # With a batched evaluator one more coalition costs a slice of a launch, while a cache miss
                 # inside the walk below costs a launch of its own plus a host read: evaluate every prefix of
                 # the sweep whose permutation survived level 2 up front.  The truncation rule still decides

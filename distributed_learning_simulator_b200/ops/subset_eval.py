@@ -95,7 +95,8 @@ class _LeNet5BatchEvaluator:
         self.device = next(iter(flats.values())).flat.device
         self.max_coalitions = int(server.config.algorithm_kwargs.get("subset_eval_chunk", 32))
         self.pad = int(server.tester.model.conv1.padding[0])
-        self.fused = bool(server.config.algorithm_kwargs.get("subset_eval_fused", True))
+        # the coalition GEMM keeps the workers' arena pointers in shared memory: at most 64 of them
+        self.fused = bool(server.config.algorithm_kwargs.get("subset_eval_fused", True)) and len(flats) <= 64
         # the fused path walks the test set in large slices (GEMM M dimension = samples x positions)
         self.eval_batch = int(server.config.algorithm_kwargs.get("subset_eval_batch", 1024))
         self._patch_cache: dict = {}
