@@ -95,3 +95,40 @@ def test_hierarchical_efficiency_and_groups():
     assert h.evaluations <= 2 ** 3 - 1 + 3 * (2 ** 2 - 1)
     h2 = HierarchicalShapleyValue(players=list(range(7)), part_number=2, vp_size=3)
     assert max(len(g) for g in h2.groups) <= 3
+
+
+def test_gtg_speculative_prefetch_gives_the_sequential_values():
+    """With a batched evaluator the GTG engine evaluates every prefix of a sweep up front and applies the
+    truncation rule afterwards: Shapley values, best subset and the random permutation stream are those
+    of the strictly sequential walk; only the number of utility evaluations grows."""
+    from distributed_learning_simulator_b200.algorithm.shapley_value.gtg_shapley_value import GTGShapleyValue
+
+    weights = {0: 0.30, 1: 0.05, 2: 0.22, 3: 0.0005, 4: 0.12, 5: 0.18}
+
+    def utility(subset):
+        s = sum(weights[p] for p in subset)
+        return 0.1 + 0.8 * (1 - (1 - s) ** 2)  # concave: later members add less, so truncation kicks in
+
+    results = {}
+    for mode in ("sequential", "batched", "batched_no_speculation"):
+        calls = {"single": 0, "batched": 0}
+
+        def single(subset):
+            calls["single"] += 1
+            return utility(subset)
+
+        def batch(subsets):
+            calls["batched"] += len(subsets)
+            return [utility(s) for s in subsets]
+
+        engine = GTGShapleyValue(players=list(weights), last_round_metric=0.1, seed=7,
+                                 speculative_prefetch=(mode == "batched"))
+        engine.set_metric_function(single)
+        engine.set_batch_metric_function(None if mode == "sequential" else batch)
+        engine.compute(round_number=1)
+        results[mode] = (dict(engine.shapley_values), dict(engine.shapley_values_S), dict(calls))
+    seq, spec, plain = results["sequential"], results["batched"], results["batched_no_speculation"]
+    assert seq[0] == spec[0] == plain[0] and seq[1] == spec[1] == plain[1]
+    assert seq[2]["batched"] == 0 and spec[2]["single"] == 0 and plain[2]["single"] == 0
+    assert spec[2]["batched"] >= plain[2]["batched"] >= 1
+    assert abs(sum(seq[0].values()) - (utility(weights) - 0.1)) < 0.05  # efficiency, up to truncation
