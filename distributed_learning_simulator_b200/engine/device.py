@@ -108,6 +108,35 @@ class CaptureGuard:
                 g._capturing = False
                 g._cond.notify_all()
 
+    class _Released:
+        """Temporarily gives up this thread's shared hold (if any) around a blocking wait for another role,
+        so that a pending capture - which stops new sharers - can never be part of a wait cycle."""
+
+        def __init__(self, guard: "CaptureGuard") -> None:
+            self.guard = guard
+            self.depth = 0
+
+        def __enter__(self) -> None:
+            g = self.guard
+            self.depth = getattr(g._local, "depth", 0)
+            if self.depth > 0:
+                g._local.depth = 0
+                with g._cond:
+                    g._sharers -= 1
+                    g._cond.notify_all()
+
+        def __exit__(self, *exc: object) -> None:
+            g = self.guard
+            if self.depth > 0:
+                with g._cond:
+                    while g._capturing or g._waiting_captures:
+                        g._cond.wait()
+                    g._sharers += 1
+                g._local.depth = self.depth
+
+    def released(self) -> "CaptureGuard._Released":
+        return CaptureGuard._Released(self)
+
     def shared(self) -> "CaptureGuard._Shared":
         return CaptureGuard._Shared(self)
 

@@ -175,13 +175,14 @@ class ModelExecutor(HookCollection):
         self._model.eval()
         with self._stream_context():
             self._model_util.refresh_shadow()  # the fp32 arena may have been written in place since
-        with capture_guard.shared(), torch.no_grad(), self._stream_context():
-            metric.start_epoch(self._device)
-            if self._dc.get_dataset_size(phase) > 0:
-                for batch in self._loader(phase):
-                    output, loss = self._forward(batch)
-                    metric.add_batch(loss, output, batch.targets)
-            if reducer is not None:
+        with torch.no_grad(), self._stream_context():
+            with capture_guard.shared():
+                metric.start_epoch(self._device)
+                if self._dc.get_dataset_size(phase) > 0:
+                    for batch in self._loader(phase):
+                        output, loss = self._forward(batch)
+                        metric.add_batch(loss, output, batch.targets)
+            if reducer is not None:  # a collective with other ranks: never while holding the guard
                 reducer.all_reduce_sum(metric.accumulator)
             metric.end_epoch(1)
         self._model.train(was_training)

@@ -96,8 +96,7 @@ class Trainer(ModelExecutor):
             with self._stream_context():
                 self.exec_hooks(ExecutorHookPoint.BEFORE_EXECUTE, executor=self)
                 if self._needs_eager():
-                    with capture_guard.shared():
-                        self._train_eager()
+                    self._train_eager()
                 else:
                     self._train_graph()
                 self.exec_hooks(ExecutorHookPoint.AFTER_EXECUTE, executor=self, epoch=self._hyper_parameter.epoch)
@@ -140,10 +139,14 @@ class Trainer(ModelExecutor):
             self._metric.start_epoch(self._device)
             for batch_index, batch in enumerate(loader):
                 self.exec_hooks(ExecutorHookPoint.BEFORE_BATCH, executor=self, epoch=epoch, batch_index=batch_index)
-                optimizer.zero_grad(set_to_none=self._model_util.flat_gradient is None)
-                output, loss = self._forward(batch)
+                # library-backed eager work holds the capture guard shared, one batch at a time and never
+                # across a hook that may wait for another role (a pending capture blocks new sharers)
+                with capture_guard.shared():
+                    optimizer.zero_grad(set_to_none=self._model_util.flat_gradient is None)
+                    output, loss = self._forward(batch)
                 self.exec_hooks(ExecutorHookPoint.AFTER_FORWARD, executor=self, epoch=epoch, batch_index=batch_index)
-                loss.backward()
+                with capture_guard.shared():
+                    loss.backward()
                 if self.has_hook(ExecutorHookPoint.OPTIMIZER_STEP):
                     # the hook owns the update (sign_SGD applies the server's majority vote), so the
                     # scheduler legitimately ticks without torch having seen optimizer.step()
@@ -152,7 +155,8 @@ class Trainer(ModelExecutor):
                         warnings.simplefilter("ignore", UserWarning)
                         scheduler.step()
                 else:
-                    optimizer.step()
+                    with capture_guard.shared():
+                        optimizer.step()
                     scheduler.step()
                 self._metric.add_batch(loss, output, batch.targets)
                 self.exec_hooks(ExecutorHookPoint.AFTER_BATCH, executor=self, epoch=epoch, batch_index=batch_index,

@@ -3,6 +3,7 @@
 the endpoint's condition variable instead of the reference's 0.1 s polling loop."""
 from typing import Any
 
+from ..engine.device import capture_guard
 from .worker import Worker
 
 
@@ -13,6 +14,9 @@ class Client(Worker):
     def _get_data_from_server(self) -> Any:
         self._release_device_lock()
         timeout = getattr(self.config, "round_timeout", None)
-        if not self._endpoint.wait_for_data(timeout=timeout):
-            raise TimeoutError(f"{self.name}: no answer from the server within {timeout}s")
+        # a worker that waits inside an eager section (the graph workers exchange embeddings from forward
+        # hooks) must not keep the capture guard: another role's graph capture may be what everybody waits for
+        with capture_guard.released():
+            if not self._endpoint.wait_for_data(timeout=timeout):
+                raise TimeoutError(f"{self.name}: no answer from the server within {timeout}s")
         return self._endpoint.get()

@@ -100,3 +100,42 @@ def test_capture_guard_excludes_eager_sections():
         t.join(timeout=60)
     assert not any(t.is_alive() for t in threads)
     assert state["violations"] == 0 and state["max_shared"] >= 2
+
+
+def test_capture_guard_released_breaks_wait_cycles():
+    """A role that blocks on another role while inside an eager section gives its hold up: a pending
+    capture (which stops NEW sharers) then cannot close a wait cycle."""
+    import threading
+    import time
+
+    from distributed_learning_simulator_b200.engine.device import CaptureGuard
+
+    guard = CaptureGuard()
+    answered = threading.Event()
+    order = []
+
+    def waiting_worker() -> None:           # holds shared, then waits for the peer's answer
+        with guard.shared():
+            with guard.released():
+                assert answered.wait(timeout=20)
+            order.append("worker resumed")
+
+    def capturer() -> None:
+        time.sleep(0.1)
+        with guard.exclusive():
+            order.append("capture")
+            time.sleep(0.05)
+
+    def peer() -> None:                     # needs the guard shared before it can answer
+        time.sleep(0.2)
+        with guard.shared():
+            order.append("peer evaluated")
+        answered.set()
+
+    threads = [threading.Thread(target=f) for f in (waiting_worker, capturer, peer)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(timeout=30)
+    assert not any(t.is_alive() for t in threads), "wait cycle"
+    assert order.index("capture") < order.index("worker resumed") and "peer evaluated" in order
