@@ -149,11 +149,12 @@ extern "C" int dls_block_sqdiff(const float* cur, const float* prev, const long 
 // The reference has no counterpart (it runs each coalition through an eager torch convolution,
 // server/server.py:40-55); torch's unfold took 80 % of the batched evaluator before this kernel.
 namespace dls {
-template <typename T>
+template <typename T, bool kPadded>
 __global__ void __launch_bounds__(256)
 im2col_grouped_kernel(const T* __restrict__ x, int batch, int height, int width, int groups, int channels, int k,
-                      int k_pad, int channels_last_k, T* __restrict__ cols) {
-    const int oh_n = height - k + 1, ow_n = width - k + 1;
+                      int k_pad, int channels_last_k, int pad, T* __restrict__ cols) {
+    // kPadded: zero padding of `pad` pixels on every border (taps outside the image contribute zeros)
+    const int oh_n = height + 2 * pad - k + 1, ow_n = width + 2 * pad - k + 1;
     const long long rows = (long long)batch * oh_n * ow_n;
     const long long total = (long long)groups * rows * k * k;
     const int kk = k * k;
@@ -166,9 +167,19 @@ im2col_grouped_kernel(const T* __restrict__ x, int batch, int height, int width,
         const int ow = (int)(row % ow_n), oh = (int)((row / ow_n) % oh_n);
         const int b = (int)(row / ((long long)ow_n * oh_n));
         const int kh = tap / k, kw = tap - kh * k;
-        const T* src = x + (((long long)b * height + oh + kh) * width + ow + kw) * ((long long)groups * channels) +
-                       (long long)g * channels;
+        const int iy = oh + kh - pad, ix = ow + kw - pad;
         T* dst_row = cols + row_g * k_pad;
+        if (kPadded && (iy < 0 || iy >= height || ix < 0 || ix >= width)) {
+            if (channels_last_k)
+                for (int c = 0; c < channels; ++c) dst_row[tap * channels + c] = T(0);
+            else
+                for (int c = 0; c < channels; ++c) dst_row[c * kk + tap] = T(0);
+            if (tap == kk - 1)
+                for (int j = channels * kk; j < k_pad; ++j) dst_row[j] = T(0);
+            continue;
+        }
+        const T* src = x + (((long long)b * height + iy) * width + ix) * ((long long)groups * channels) +
+                       (long long)g * channels;
         if (channels_last_k) {
             T* dst = dst_row + tap * channels;
             if (sizeof(T) == 2 && (channels & 1) == 0 && (k_pad & 1) == 0) {
@@ -195,11 +206,31 @@ extern "C" int dls_im2col_grouped(const void* x, int elem_bytes, int batch, int 
     const long long total = (long long)groups * batch * (height - k + 1) * (width - k + 1) * k * k;
     const int grid = dls::grid_for(total, 256, 16);
     if (elem_bytes == 2)
-        dls::im2col_grouped_kernel<uint16_t><<<grid, 256, 0, (cudaStream_t)stream>>>(
-            (const uint16_t*)x, batch, height, width, groups, channels, k, k_pad, channels_last_k, (uint16_t*)cols);
+        dls::im2col_grouped_kernel<uint16_t, false><<<grid, 256, 0, (cudaStream_t)stream>>>(
+            (const uint16_t*)x, batch, height, width, groups, channels, k, k_pad, channels_last_k, 0, (uint16_t*)cols);
     else
-        dls::im2col_grouped_kernel<uint32_t><<<grid, 256, 0, (cudaStream_t)stream>>>(
-            (const uint32_t*)x, batch, height, width, groups, channels, k, k_pad, channels_last_k, (uint32_t*)cols);
+        dls::im2col_grouped_kernel<uint32_t, false><<<grid, 256, 0, (cudaStream_t)stream>>>(
+            (const uint32_t*)x, batch, height, width, groups, channels, k, k_pad, channels_last_k, 0, (uint32_t*)cols);
+    DLS_LAUNCHED("im2col_grouped_kernel");
+    return 0;
+}
+
+extern "C" int dls_im2col_grouped_padded(const void* x, int elem_bytes, int batch, int height, int width, int groups,
+                                         int channels, int k, int k_pad, int channels_last_k, int pad, void* cols,
+                                         void* stream) {
+    if (pad < 0 || batch < 1 || groups < 1 || channels < 1 || k < 1 || height + 2 * pad < k || width + 2 * pad < k ||
+        k_pad < channels * k * k)
+        return dls::fail_msg("dls_im2col_grouped_padded: bad shape");
+    if (elem_bytes != 2 && elem_bytes != 4) return dls::fail_msg("dls_im2col_grouped_padded: 2- or 4-byte elements");
+    const long long total =
+        (long long)groups * batch * (height + 2 * pad - k + 1) * (width + 2 * pad - k + 1) * k * k;
+    const int grid = dls::grid_for(total, 256, 16);
+    if (elem_bytes == 2)
+        dls::im2col_grouped_kernel<uint16_t, true><<<grid, 256, 0, (cudaStream_t)stream>>>(
+            (const uint16_t*)x, batch, height, width, groups, channels, k, k_pad, channels_last_k, pad, (uint16_t*)cols);
+    else
+        dls::im2col_grouped_kernel<uint32_t, true><<<grid, 256, 0, (cudaStream_t)stream>>>(
+            (const uint32_t*)x, batch, height, width, groups, channels, k, k_pad, channels_last_k, pad, (uint32_t*)cols);
     DLS_LAUNCHED("im2col_grouped_kernel");
     return 0;
 }

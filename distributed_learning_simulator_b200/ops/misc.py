@@ -91,28 +91,35 @@ def oracle_block_sqdiff(cur, prev, tensor_offsets, block_of_tensor, n_blocks) ->
     return scores
 
 
-def im2col_grouped(x_nhwc: torch.Tensor, groups: int, k: int, channels_last_k: bool, k_pad: int | None = None) -> torch.Tensor:
-    """x_nhwc: [B, H, W, groups * C] contiguous.  Returns cols [groups, B*OH*OW, k_pad] for valid k x k
-    windows; column order (kh, kw, c) if ``channels_last_k`` else (c, kh, kw)."""
+def im2col_grouped(x_nhwc: torch.Tensor, groups: int, k: int, channels_last_k: bool, k_pad: int | None = None,
+                   pad: int = 0) -> torch.Tensor:
+    """x_nhwc: [B, H, W, groups * C] contiguous.  Returns cols [groups, B*OH*OW, k_pad] for k x k windows with
+    ``pad`` pixels of zero padding; column order (kh, kw, c) if ``channels_last_k`` else (c, kh, kw)."""
     b, h, w, gc = x_nhwc.shape
     c = gc // groups
     assert gc == groups * c and x_nhwc.is_contiguous()
     kk = c * k * k
     if k_pad is None:
         k_pad = kk + (-kk) % 8
+    oh, ow = h + 2 * pad - k + 1, w + 2 * pad - k + 1
     if x_nhwc.is_cuda and runtime.available() and x_nhwc.element_size() in (2, 4):
-        cols = torch.empty((groups, b * (h - k + 1) * (w - k + 1), k_pad), dtype=x_nhwc.dtype, device=x_nhwc.device)
-        runtime.call("dls_im2col_grouped", x_nhwc.data_ptr(), x_nhwc.element_size(), b, h, w, groups, c, k, k_pad,
-                     int(channels_last_k), cols.data_ptr(), runtime.stream_ptr(x_nhwc.device))
+        cols = torch.empty((groups, b * oh * ow, k_pad), dtype=x_nhwc.dtype, device=x_nhwc.device)
+        if pad == 0:
+            runtime.call("dls_im2col_grouped", x_nhwc.data_ptr(), x_nhwc.element_size(), b, h, w, groups, c, k, k_pad,
+                         int(channels_last_k), cols.data_ptr(), runtime.stream_ptr(x_nhwc.device))
+        else:
+            runtime.call("dls_im2col_grouped_padded", x_nhwc.data_ptr(), x_nhwc.element_size(), b, h, w, groups, c, k,
+                         k_pad, int(channels_last_k), int(pad), cols.data_ptr(), runtime.stream_ptr(x_nhwc.device))
         return cols
-    return oracle_im2col_grouped(x_nhwc, groups, k, channels_last_k, k_pad)
+    return oracle_im2col_grouped(x_nhwc, groups, k, channels_last_k, k_pad, pad)
 
 
-def oracle_im2col_grouped(x_nhwc: torch.Tensor, groups: int, k: int, channels_last_k: bool, k_pad: int) -> torch.Tensor:
+def oracle_im2col_grouped(x_nhwc: torch.Tensor, groups: int, k: int, channels_last_k: bool, k_pad: int,
+                          pad: int = 0) -> torch.Tensor:
     b, h, w, gc = x_nhwc.shape
     c = gc // groups
-    oh, ow = h - k + 1, w - k + 1
-    cols = torch.nn.functional.unfold(x_nhwc.permute(0, 3, 1, 2).float(), k).view(b, groups, c, k * k, oh * ow)
+    oh, ow = h + 2 * pad - k + 1, w + 2 * pad - k + 1
+    cols = torch.nn.functional.unfold(x_nhwc.permute(0, 3, 1, 2).float(), k, padding=pad).view(b, groups, c, k * k, oh * ow)
     cols = cols.permute(1, 0, 4, 3, 2) if channels_last_k else cols.permute(1, 0, 4, 2, 3)
     cols = cols.reshape(groups, b * oh * ow, c * k * k).to(x_nhwc.dtype)
     return torch.nn.functional.pad(cols, (0, k_pad - c * k * k))

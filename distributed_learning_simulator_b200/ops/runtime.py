@@ -66,6 +66,8 @@ _SIGNATURES = {
     "dls_subset_gemm_bf16": [c_void_p, c_int, c_void_p, c_int, c_ll, c_ll, c_void_p, c_int, c_int, c_int, c_void_p,
                              c_int, c_int, c_int, c_int, c_int, c_int, c_void_p],
     "dls_im2col_grouped": [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p],
+    "dls_im2col_grouped_padded": [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p,
+                                  c_void_p],
     "dls_index_compact": [c_void_p, c_void_p, c_ll, c_void_p, c_void_p, c_float, c_u64, c_void_p, c_void_p, c_void_p,
                           c_void_p, c_void_p, c_void_p],
     "dls_row_gather": [c_void_p, c_void_p, c_ll, c_ll, c_void_p, c_void_p],

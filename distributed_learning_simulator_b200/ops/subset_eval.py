@@ -138,10 +138,9 @@ class _LeNet5BatchEvaluator:
         hw = x.shape[-1] + 2 * self.pad - k1 + 1
         cols = self._patch_cache.get(cache_key) if cache_key is not None else None
         if cols is None:  # first-layer patches do not depend on the coalition: built once per test slice
-            cols = F.unfold(x, k1, padding=self.pad).transpose(1, 2).reshape(B * hw * hw, -1)
-            if self.layout.formats[w1]:  # filters stored (o, kh, kw, c): reorder the patch columns to match
-                cols = cols.view(B * hw * hw, -1, k1 * k1).transpose(1, 2).reshape(B * hw * hw, -1)
-            cols = torch.nn.functional.pad(cols.to(torch.bfloat16), (0, (-cols.shape[1]) % 8)).contiguous()
+            # own im2col (zero padding handled in the kernel), bf16, K padded to 8, the arena's filter order
+            nhwc = x.to(torch.bfloat16).permute(0, 2, 3, 1).contiguous()
+            cols = misc.im2col_grouped(nhwc, 1, k1, bool(self.layout.formats[w1]), pad=self.pad)[0]
             if cache_key is not None:
                 self._patch_cache[cache_key] = cols
         if mark: mark("patches1")

@@ -185,6 +185,9 @@ int dls_subset_gemm_bf16(const void* a, int a_shared, const float* const* worker
  * zero beyond channels*k*k.  elem_bytes 2 (bf16/fp16) or 4. */
 int dls_im2col_grouped(const void* x, int elem_bytes, int batch, int height, int width, int groups, int channels,
                        int k, int k_pad, int channels_last_k, void* cols, void* stream);
+/* Same with `pad` pixels of zero padding on every border (rows = B * (H + 2 pad - k + 1) * (W + 2 pad - k + 1)). */
+int dls_im2col_grouped_padded(const void* x, int elem_bytes, int batch, int height, int width, int groups,
+                              int channels, int k, int k_pad, int channels_last_k, int pad, void* cols, void* stream);
 
 /* ---- graph family: fed_gnn / fed_gcn / fed_aas (reference: worker/graph_worker.py:205-216,
  *      252-269, 271-321) ------------------------------------------------------ */

@@ -358,7 +358,8 @@ def test_im2col_grouped_matches_unfold(dev, dtype, groups, channels, k, channels
     from distributed_learning_simulator_b200.ops import misc as M
 
     x = torch.randn(7, 14, 14, groups * channels, device=dev).to(dtype)
-    got = M.im2col_grouped(x, groups, k, channels_last_k)
-    ref = M.oracle_im2col_grouped(x, groups, k, channels_last_k, got.shape[-1])
-    assert got.shape == ref.shape and got.shape[-1] % 8 == 0
-    assert torch.equal(got, ref)
+    for pad in (0, 2, 1):  # 0: the plain kernel; > 0: the zero-padding variant (LeNet-5's first layer uses 2)
+        got = M.im2col_grouped(x, groups, k, channels_last_k, pad=pad)
+        ref = M.oracle_im2col_grouped(x, groups, k, channels_last_k, got.shape[-1], pad)
+        assert got.shape == ref.shape and got.shape[-1] % 8 == 0
+        assert torch.equal(got, ref), pad
