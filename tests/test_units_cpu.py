@@ -1,0 +1,135 @@
+"""Pure-CPU unit tests of the pieces the reference never tests: closed-form FedAvg
+with full and delta uploads, quantizer round-trip bounds / unbiasedness / bit accounting, samplers."""
+import math
+
+import torch
+
+from distributed_learning_simulator_b200.engine.model_util import ParameterLayout
+
+
+def _layout(numels):
+    return ParameterLayout([f"t{i}" for i in range(len(numels))], [torch.Size([n]) for n in numels])
+
+
+def test_fed_avg_closed_form_full_and_delta_uploads():
+    """old + sum_i n_i (w_i - old) / sum n_i, whether workers send parameters or deltas, fp64 accumulation
+    (reference: algorithm/fed_avg_algorithm.py:39-52, message.py:41-49)."""
+    from distributed_learning_simulator_b200.algorithm.fed_avg_algorithm import FedAVGAlgorithm
+    from distributed_learning_simulator_b200.message import DeltaParameterMessage, ParameterMessage
+
+    g = torch.Generator().manual_seed(0)
+    old = {"a.weight": torch.randn(4, 3, generator=g), "a.bias": torch.randn(4, generator=g)}
+    sizes = [10, 30, 60]
+    new = [{k: v + torch.randn(v.shape, generator=g) for k, v in old.items()} for _ in sizes]
+    want = {k: sum(n * w[k].double() for n, w in zip(sizes, new)) / sum(sizes) for k in old}
+    for mode in ("full", "delta", "mixed"):
+        algo = FedAVGAlgorithm()
+        for i, (n, w) in enumerate(zip(sizes, new)):
+            as_delta = mode == "delta" or (mode == "mixed" and i % 2 == 1)
+            if as_delta:
+                msg = DeltaParameterMessage(dataset_size=n, delta_parameter={k: w[k] - old[k] for k in old})
+            else:
+                msg = ParameterMessage(dataset_size=n, parameter={k: v.clone() for k, v in w.items()})
+            algo.process_worker_data(i, msg, save_dir="", old_parameter_dict=old)
+        result = algo.aggregate_worker_data()
+        assert isinstance(result, ParameterMessage)
+        for k in old:
+            torch.testing.assert_close(result.parameter[k].double(), want[k], rtol=1e-6, atol=1e-6)
+        assert not result.end_training
+
+
+def test_fed_avg_skips_absent_workers_and_propagates_end_training():
+    from distributed_learning_simulator_b200.algorithm.fed_avg_algorithm import FedAVGAlgorithm
+    from distributed_learning_simulator_b200.message import ParameterMessage
+
+    old = {"w": torch.zeros(5)}
+    algo = FedAVGAlgorithm()
+    algo.process_worker_data(0, ParameterMessage(dataset_size=1, parameter={"w": torch.ones(5)}, end_training=True),
+                             save_dir="", old_parameter_dict=old)
+    algo.process_worker_data(1, None, save_dir="", old_parameter_dict=old)  # not selected this round
+    algo.process_worker_data(2, ParameterMessage(dataset_size=3, parameter={"w": torch.full((5,), 5.0)}),
+                             save_dir="", old_parameter_dict=old)
+    result = algo.aggregate_worker_data()
+    torch.testing.assert_close(result.parameter["w"], torch.full((5,), 4.0))
+    assert result.end_training
+
+
+def test_stochastic_quantization_is_bounded_and_unbiased():
+    """8-bit stochastic quantization per tensor (fed_paq / fed_obd_sq): |x - deq(q(x))| <= max|x| / 255 and
+    E[deq(q(x))] = x; zero tensors and signs survive."""
+    from distributed_learning_simulator_b200.algorithm.quantization.stochastic import sq_dequantize_flat, sq_quantize_flat
+
+    layout = _layout([1000, 7, 64, 1])
+    g = torch.Generator().manual_seed(1)
+    flat = torch.randn(layout.total, generator=g) * torch.tensor([3.0] * 1000 + [0.0] * 7 + [0.01] * 64 + [5.0])
+    mean = torch.zeros_like(flat)
+    reps = 200
+    for r in range(reps):
+        q = sq_quantize_flat(flat, layout, 255, generator=torch.Generator().manual_seed(100 + r))
+        deq = sq_dequantize_flat(q)
+        for i in range(len(layout.names)):
+            seg = slice(layout.offsets[i], layout.offsets[i + 1])
+            bound = float(flat[seg].abs().max()) / 255 + 1e-7
+            assert float((deq[seg] - flat[seg]).abs().max()) <= bound
+        assert torch.equal(torch.sign(deq) * (deq != 0), torch.sign(flat) * (deq != 0))
+        mean += deq / reps
+    assert q.payload.dtype == torch.uint8 and q.payload.numel() == layout.total
+    step = 3.0 * 4 / 255  # loose per-element step of the big tensor
+    assert float((mean - flat).abs().max()) < 4 * step / math.sqrt(reps) + 1e-3
+    assert float(mean[1000:1007].abs().max()) == 0.0
+
+
+def test_nnadq_round_trip_error_follows_the_chosen_bit_width():
+    """NNADQ (fed_obd): per tensor, error <= step / 2 with step = range / (2^bits - 1); a larger weight
+    (tolerance) buys fewer bits and a smaller payload."""
+    from distributed_learning_simulator_b200.algorithm.quantization.deterministic import (nnadq_dequantize_flat,
+                                                                                          nnadq_quantize_flat)
+
+    layout = _layout([4096, 33, 5, 1024])
+    g = torch.Generator().manual_seed(2)
+    flat = torch.randn(layout.total, generator=g)
+    flat[4096 + 33: 4096 + 38] = 0.25  # a constant tensor: range 0
+    sizes = {}
+    for weight in (0.001, 0.01, 0.1):
+        q = nnadq_quantize_flat(flat, layout, weight)
+        deq = nnadq_dequantize_flat(q)
+        for i in range(len(layout.names)):
+            seg = slice(layout.offsets[i], layout.offsets[i + 1])
+            rng = float(flat[seg].max() - flat[seg].min())
+            bits = int(q.bits[i])
+            assert 1 <= bits <= 16
+            step = rng / (2 ** bits - 1) if rng > 0 else 0.0
+            assert float((deq[seg] - flat[seg]).abs().max()) <= step / 2 + 1e-6, (weight, i, bits)
+        sizes[weight] = int(q.payload.numel())
+        assert int(q.byte_offsets[-1]) == q.payload.numel()
+    assert sizes[0.001] > sizes[0.01] > sizes[0.1]
+    assert sizes[0.1] < layout.total * 4 / 3  # well under fp32
+
+
+def test_random_label_iid_split_covers_every_label_and_partitions_the_samples():
+    """``random_label_iid`` (reference: sampler/base.py:9-46): each part holds exactly the requested number of
+    classes, every class is held by somebody, and no training sample is given to two parts."""
+    import random
+
+    from distributed_learning_simulator_b200 import load_config_from_dict
+    from distributed_learning_simulator_b200.engine.ml_type import MachineLearningPhase
+
+    random.seed(3)
+    config = load_config_from_dict({
+        "dataset_name": "MNIST", "model_name": "LeNet5", "distributed_algorithm": "fed_avg", "worker_number": 5,
+        "round": 1, "epoch": 1, "log_level": "WARNING", "dataset_sampling": "random_label_iid",
+        "dataset_sampling_kwargs": {"sampled_class_number": 4},
+        "dataset_kwargs": {"train_size": 2000, "test_size": 100}})
+    practitioners = config.create_practitioners()
+    seen: set = set()
+    labels_seen: set = set()
+    for p in sorted(practitioners, key=lambda p: p.worker_id):
+        trainer = p.create_trainer(config)
+        util = trainer.dataset_collection.get_dataset_util(MachineLearningPhase.Training)
+        indices = set(int(i) for i in util.indices)
+        assert indices and not (indices & seen)
+        seen |= indices
+        labels = set(int(t) for t in util.targets[util.indices])
+        assert len(labels) <= 4
+        labels_seen |= labels
+    assert labels_seen == set(range(10))
