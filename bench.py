@@ -174,9 +174,13 @@ def run_ours(args) -> dict:
 
 
 def run_reference(args) -> dict:
-    ref_dir = os.path.join(ROOT, "baseline", "_ref")
-    if not os.path.isdir(os.path.join(ref_dir, "distributed_learning_simulator")):
-        return {"impl": "reference", "unavailable": "baseline/_ref is not installed (pip --target baseline/_ref)"}
+    from baseline.install_ref import ReferenceUnavailable, ensure_installed
+
+    try:
+        if int(os.environ.get("LOCAL_RANK", "0")) == 0:
+            ensure_installed()
+    except ReferenceUnavailable as e:
+        return {"impl": "reference", "unavailable": str(e)[:300].replace("\n", " "), "exit_code": 1}
     try:
         from baseline.reference_arm import run as run_ref
     except Exception as e:  # noqa: BLE001
@@ -193,8 +197,11 @@ def main() -> None:
     args = ap.parse_args()
     assert args.warmup >= 3 or args.impl == "reference" or os.environ.get("DLS_BENCH_ALLOW_SHORT"), "warmup >= 3"
     result = run_reference(args) if args.impl == "reference" else run_ours(args)
+    exit_code = int(result.pop("exit_code", 0)) if isinstance(result, dict) else 0
     if int(os.environ.get("RANK", "0")) == 0:
         print(json.dumps(result), flush=True)
+    if exit_code:
+        sys.exit(exit_code)
 
 
 if __name__ == "__main__":

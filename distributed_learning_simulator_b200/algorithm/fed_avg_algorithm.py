@@ -48,7 +48,9 @@ class FedAVGAlgorithm(AggregationAlgorithm):
         if self.accumulate and self.use_fused and self.fused_variant is not None:
             from ..ops import reduce as reduce_ops
 
-            if reduce_ops.can_fuse(worker_data, old_parameter_dict):
+            # only while nothing went down the streaming path this round: the two accumulators are
+            # never live together (a fusable upload after a non-fusable one is streamed as well)
+            if not self.__parameter and reduce_ops.can_fuse(worker_data, old_parameter_dict):
                 # defer: the kernel consumes the raw (possibly delta / packed) rows
                 self.__pending[worker_id] = worker_data
                 self._all_worker_data[worker_id] = worker_data

@@ -104,7 +104,11 @@ class NeuralNetworkAdaptiveDeterministicQuant:
     def check_compression_ratio(cls, quantized_data: Any, prefix: str) -> float:
         """Logs ``<prefix> NNABQ compression ratio is <float>`` -- the float must stay the
         last token: analysis/analyze_log.py scrapes it (reference analyze_log.py:108-113,131-134)."""
-        payload = getattr(quantized_data, "parameter", quantized_data)
+        payload = quantized_data
+        for field in ("parameter", "delta_parameter"):  # FedOBD phase-2 uploads are DeltaParameterMessages
+            if hasattr(quantized_data, field):
+                payload = getattr(quantized_data, field)
+                break
         q = payload.get("__quantized__") if isinstance(payload, dict) else None
         ratio = q.compression_ratio() if q is not None else 1.0
         get_logger().info("%s NNABQ compression ratio is %s", prefix, ratio)

@@ -72,7 +72,20 @@ class GradientWorker(Client):
         hp = trainer.hyper_parameter
         params = [p for p in trainer.model.parameters()]
         grads = [p.grad if p.grad is not None else torch.zeros_like(p) for p in params]
-        gradient = torch.cat([g.reshape(-1) for g in compute_gradient(params, grads, hp.weight_decay)])
+        real = compute_gradient(params, grads, hp.weight_decay)
+        flat = trainer.model_util.flat_parameter
+        arena_order = flat is not None and flat.is_cuda and runtime.available()
+        if arena_order:
+            # the fused update walks the arena, whose 4-D segments are stored channels-last: the
+            # exchanged vector must be in that physical order, not the logical (o, c, h, w) one
+            layout = trainer.model_util.layout
+            names = [n for n, _ in trainer.model.named_parameters()]
+            assert names == layout.names
+            gradient = torch.empty(layout.total, dtype=torch.float32, device=flat.device)
+            for i, g in enumerate(real):
+                layout.view_of(gradient, i).copy_(g)
+        else:
+            gradient = torch.cat([g.reshape(-1) for g in real])
         self.send_data_to_server(GradientMessage(
             in_round=True, other_data={"dataset_size": trainer.dataset_size, "gradient": self._process_gradient(gradient),
                                        "numel": gradient.numel()}))
@@ -80,11 +93,10 @@ class GradientWorker(Client):
         assert result is not None
         d_p = self._decode_gradient(result.other_data["gradient"], gradient.numel()).to(gradient.device)
         lr = trainer.current_lr()
-        flat = trainer.model_util.flat_parameter
         if self.__momentum_buf is None or self.__momentum_buf.device != gradient.device:
             self.__momentum_buf = torch.zeros_like(gradient)
             self.__step = 0
-        if flat is not None and flat.is_cuda and runtime.available():
+        if arena_order:
             dev = flat.device
             if self.__state is None or self.__state.device != dev:
                 self.__state = torch.zeros(4, dtype=torch.int32, device=dev)
