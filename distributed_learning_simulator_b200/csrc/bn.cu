@@ -666,6 +666,37 @@ extern "C" int dls_bn_fwd(const void* x, int dtype, long long rows, int channels
     return 0;
 }
 
+// Forward pass when the producing convolution already accumulated the channel statistics in its epilogue
+// (stats = fp32 [2][channels]: sum, sum of squares): the reduction launch disappears, one elementwise launch
+// builds scale / shift from the sums and applies normalisation (+ residual) (+ ReLU).
+extern "C" int dls_bn_fwd_stats(const void* x, int dtype, long long rows, int channels, const float* gamma,
+                                const float* beta, const void* residual, float eps, int relu, void* y, float* mean,
+                                float* invstd, const float* stats, void* stream) {
+    BnPlan p;
+    if (int rc = bn_plan(rows, channels, dtype, &p)) return rc;
+    if (stats == nullptr) return fail_msg("dls_bn_fwd_stats: stats is NULL");
+    const int cv = channels / p.v;
+    if (cv > kWideThreads) return fail_msg("dls_bn_fwd_stats: too many channels for one row per CTA pass");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int rows_per_iter = kWideThreads / cv;
+    long long grid = (rows + (long long)rows_per_iter * 4 - 1) / ((long long)rows_per_iter * 4);
+    if (grid > 2 * kNumSMs) grid = 2 * kNumSMs;
+    if (grid < 1) grid = 1;
+    const size_t smem = (size_t)2 * channels * sizeof(float);
+    cudaError_t e;
+#define DLS_BN_APPLY(T, V)                                                                                         \
+    e = wide_launch(bn_wide_apply_kernel<T, V, false>, (int)grid, 1, smem, s, (const T*)x, (const T*)nullptr,     \
+                    (const T*)residual, rows, channels, gamma, beta, eps, relu, stats, 1, mean, invstd,            \
+                    (float*)nullptr, (float*)nullptr, (T*)y, (T*)nullptr)
+    if (dtype == 1 && p.v == 8) DLS_BN_APPLY(__nv_bfloat16, 8);
+    else if (dtype == 1) DLS_BN_APPLY(__nv_bfloat16, 4);
+    else DLS_BN_APPLY(float, 4);
+#undef DLS_BN_APPLY
+    if (e != cudaSuccess) return fail("bn_wide_apply_kernel", e);
+    DLS_LAUNCHED("bn_wide_apply_kernel");
+    return 0;
+}
+
 extern "C" int dls_bn_bwd(const void* dy, const void* y, const void* x, int dtype, long long rows, int channels,
                           const float* gamma, const float* mean, const float* invstd, int relu, void* dx,
                           void* dresidual, float* dgamma, float* dbeta, float* scratch, void* stream) {

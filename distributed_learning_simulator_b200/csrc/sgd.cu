@@ -39,7 +39,11 @@ sgd_step_kernel(float* __restrict__ params, float* __restrict__ mom, const float
         const long long j = i - s_off[t];
         const bool fast = (i + 4 <= s_off[t + 1]) && ((j & 3) == 0) && grads[t] != nullptr;
         float g[4], p[4], m[4];
-        const bool half_grad = grad_is_bf16 != nullptr && grad_is_bf16[t] != 0;
+        // per-tensor flags: bit 0 = bf16 gradient, bits 0|1 = the model's matrix is the bf16 shadow (rewrite
+        // it), bit 2 = fp32 gradient sink that accumulates (conv wgrad partial tiles): zero it after reading
+        const uint8_t flags = grad_is_bf16 != nullptr ? grad_is_bf16[t] : (uint8_t)0;
+        const bool half_grad = (flags & 1) != 0;
+        const bool has_shadow = (flags & 3) != 0;
         if (fast) {
             if (half_grad) {  // mixed precision: the model's matrix is the bf16 shadow, so is its gradient
                 const uint2 raw = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(grads[t]) + j);
@@ -47,8 +51,15 @@ sgd_step_kernel(float* __restrict__ params, float* __restrict__ mom, const float
                 const float2 hi = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.y));
                 g[0] = lo.x; g[1] = lo.y; g[2] = hi.x; g[3] = hi.y;
             } else {
-                const float4 gv = ld_stream_f4(grads[t] + j);  // gradients are read exactly once
-                g[0] = gv.x; g[1] = gv.y; g[2] = gv.z; g[3] = gv.w;
+                if (flags & 4) {
+                    float4* gp4 = reinterpret_cast<float4*>(const_cast<float*>(grads[t]) + j);
+                    const float4 gv = *gp4;
+                    *gp4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                    g[0] = gv.x; g[1] = gv.y; g[2] = gv.z; g[3] = gv.w;
+                } else {
+                    const float4 gv = ld_stream_f4(grads[t] + j);  // gradients are read exactly once
+                    g[0] = gv.x; g[1] = gv.y; g[2] = gv.z; g[3] = gv.w;
+                }
             }
             const float4 pv = *reinterpret_cast<const float4*>(params + i);
             p[0] = pv.x; p[1] = pv.y; p[2] = pv.z; p[3] = pv.w;
@@ -67,7 +78,7 @@ sgd_step_kernel(float* __restrict__ params, float* __restrict__ mom, const float
             }
             *reinterpret_cast<float4*>(params + i) = make_float4(p[0], p[1], p[2], p[3]);
             if (momentum != 0.f) *reinterpret_cast<float4*>(mom + i) = make_float4(m[0], m[1], m[2], m[3]);
-            if (half_grad && shadow != nullptr) {  // refresh the bf16 compute copy in the same pass
+            if (has_shadow && shadow != nullptr) {  // refresh the bf16 compute copy in the same pass
                 uint2 out;
                 *reinterpret_cast<__nv_bfloat162*>(&out.x) = __floats2bfloat162_rn(p[0], p[1]);
                 *reinterpret_cast<__nv_bfloat162*>(&out.y) = __floats2bfloat162_rn(p[2], p[3]);
@@ -80,9 +91,11 @@ sgd_step_kernel(float* __restrict__ params, float* __restrict__ mom, const float
                 const int te = find_segment(s_off, n_tensors, ie);
                 const float* gp = grads[te];
                 if (gp == nullptr) continue;  // parameter received no gradient this step
-                const bool half_e = grad_is_bf16 != nullptr && grad_is_bf16[te] != 0;
+                const uint8_t fe = grad_is_bf16 != nullptr ? grad_is_bf16[te] : (uint8_t)0;
+                const bool half_e = (fe & 1) != 0;
                 const float ge = half_e ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(gp)[ie - s_off[te]])
                                         : gp[ie - s_off[te]];
+                if (fe & 4) const_cast<float*>(gp)[ie - s_off[te]] = 0.f;
                 float d = ge + weight_decay * params[ie];
                 if (momentum != 0.f) {
                     const float mm = mom_ready ? momentum * mom[ie] + (1.f - dampening) * d : d;
@@ -90,7 +103,7 @@ sgd_step_kernel(float* __restrict__ params, float* __restrict__ mom, const float
                     d = nesterov ? d + momentum * mm : mm;
                 }
                 params[ie] -= lr * d;
-                if (half_e && shadow != nullptr) shadow[ie] = __float2bfloat16(params[ie]);
+                if ((fe & 3) != 0 && shadow != nullptr) shadow[ie] = __float2bfloat16(params[ie]);
             }
         }
     }

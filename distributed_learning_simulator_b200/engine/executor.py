@@ -16,6 +16,7 @@ from .hyper_parameter import HyperParameter
 from .metric import PerformanceMetric
 from .ml_type import MachineLearningPhase
 from .model_util import ModelUtil
+from ..ops import conv as conv_ops
 
 
 @dataclass
@@ -33,6 +34,7 @@ class ModelExecutor(HookCollection):
                  hyper_parameter: HyperParameter, hook_config: HookConfig | None = None) -> None:
         super().__init__()
         self._model = model
+        conv_ops.install(model)  # nn.Conv2d -> this framework's kernels on CUDA (no-op elsewhere)
         self._model_util = ModelUtil(model)
         self._dc = dataset_collection
         self._phase = phase

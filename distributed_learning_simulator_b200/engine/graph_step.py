@@ -56,8 +56,6 @@ class _CapturedStep:
 class GraphTrainStep:
     def __init__(self, trainer: Any) -> None:
         runtime.require()
-        if os.environ.get("DLS_CUDNN_BENCHMARK", "1") != "0":
-            torch.backends.cudnn.benchmark = True  # shapes are static: let cuDNN pick its fastest kernels
         self.trainer = trainer
         self.device = trainer.device
         self.util = trainer.model_util
@@ -73,10 +71,18 @@ class GraphTrainStep:
         self.shadow_flags: torch.Tensor | None = None
         if self.use_shadow:
             self.shadow_flags = torch.tensor(self.util.shadow_flags(), dtype=torch.uint8, device=self.device)
-        # weight-gradient kernels run on a side stream: a parallel branch of the captured graph (ops/conv.py)
+        # convolutions run on this framework's kernels (ops/conv.py); their weight-gradient kernels go to a
+        # side stream -- a parallel branch of the captured graph -- and write fp32 sinks that the fused SGD
+        # kernel reads in place
         self.side_stream: torch.cuda.Stream | None = None
-        if os.environ.get("DLS_SPLIT_BACKWARD", "1") != "0" and conv_ops.install(trainer.model) > 0:
+        self.wgrad_sinks: dict[int, list] = {}
+        self._sink_of_param: dict[int, list] = {}
+        n_convs = conv_ops.install(trainer.model)
+        if n_convs > 0 and os.environ.get("DLS_SPLIT_BACKWARD", "1") != "0":
             self.side_stream = torch.cuda.Stream(device=self.device)
+        self.grad_flags: torch.Tensor | None = None
+        stats_floats = sum(2 * m.out_channels for m in trainer.model.modules() if type(m) is torch.nn.Conv2d)
+        self.stats_buf = torch.zeros(stats_floats, dtype=torch.float32, device=self.device) if stats_floats else None
         # state: [0] lr/optimizer step, [1] momentum initialised, [2] batch index in epoch
         self.state = torch.zeros(4, dtype=torch.int32, device=self.device)
         self.acc = torch.zeros(3, dtype=torch.float64, device=self.device)
@@ -108,7 +114,10 @@ class GraphTrainStep:
         hp = t.hyper_parameter
         sgd_ops.gather_batch(x_all, y_all, self.order, n_order, self.state, 2, step.x, step.y,
                              batch_stride=hp.batch_size)
-        with t._autocast(), conv_ops.split_backward(self.side_stream):
+        if self.stats_buf is not None:
+            self.stats_buf.zero_()  # one fill for the BatchNorm statistics of every convolution epilogue
+        with t._autocast(), conv_ops.split_backward(self.side_stream, self.wgrad_sinks), \
+                conv_ops.stats_arena(self.stats_buf):
             output = t.model(step.x)
             loss = t.loss_fun(output.float(), step.y)
         loss.backward()
@@ -118,19 +127,49 @@ class GraphTrainStep:
             step.grad_table = torch.zeros(self.n_tensors, dtype=torch.int64, device=self.device)
         sgd_ops.sgd_step(self.flat, self.momentum_buf if hp.momentum else None, step.grad_table, self.offsets,
                          self.n_tensors, self.lr_table, self.state, hp.weight_decay, hp.momentum,
-                         grad_is_bf16=self.shadow_flags, shadow=self.shadow)
+                         grad_is_bf16=self.grad_flags, shadow=self.shadow)
         sgd_ops.sgd_tick(self.state)
         sgd_ops.metric_accumulate(output.float().contiguous(), step.y, loss.detach().reshape(1), self.acc)
+
+    def _make_sinks(self) -> None:
+        """One persistent fp32 buffer per convolution filter, in the filter's physical layout."""
+        if self.wgrad_sinks or os.environ.get("DLS_WGRAD_SINK", "1") == "0":
+            return
+        for module in self.trainer.model.modules():
+            if type(module) is torch.nn.Conv2d and getattr(module, "_dls_own_conv", False):
+                w = module.weight
+                if not w.requires_grad:
+                    continue
+                # [buffer, accumulate?]: the second entry is decided by the layer's first forward (whether
+                # its weight-gradient kernel splits the pixel range and adds partial tiles)
+                entry = [torch.zeros_like(w, dtype=torch.float32), None]
+                self.wgrad_sinks[id(module)] = entry
+                self._sink_of_param[id(w)] = entry
 
     def _fill_grad_table(self, step: _CapturedStep) -> None:
         params = list(self.trainer.model.parameters())
         step.grads = [p.grad for p in params]
-        ptrs = [0 if g is None else g.data_ptr() for g in step.grads]
-        for p, g in zip(params, step.grads):
+        ptrs, flags = [], []
+        base_flags = self.util.shadow_flags() if self.use_shadow else [0] * len(params)
+        for p, g, f in zip(params, step.grads, base_flags):
+            if g is None and id(p) in self._sink_of_param:
+                # the convolution wrote its weight gradient into the sink (fp32, accumulating): bit 2 lets
+                # the update clear it for the next step; bit 1 keeps the bf16 shadow rewrite
+                sink, accumulate = self._sink_of_param[id(p)]
+                ptrs.append(sink.data_ptr())
+                flags.append((2 if f else 0) | (4 if accumulate else 0))
+                continue
             # the fused update walks physical memory: a gradient must be laid out like its parameter
             # (autograd's layout contract gives channels-last grads for channels-last weights)
             assert g is None or (g.dtype == p.dtype and _same_physical_layout(g, p)), (g.stride(), p.stride())
+            ptrs.append(0 if g is None else g.data_ptr())
+            flags.append(f)
         step.grad_table.copy_(torch.tensor(ptrs, dtype=torch.int64))
+        new_flags = torch.tensor(flags, dtype=torch.uint8)
+        if self.grad_flags is None:
+            self.grad_flags = new_flags.to(self.device)
+        else:
+            self.grad_flags.copy_(new_flags)
 
     def _capture(self, batch: int, x_all: torch.Tensor, y_all: torch.Tensor, n_order: int) -> _CapturedStep:
         with _capture_lock():
@@ -148,7 +187,11 @@ class GraphTrainStep:
             step.x = step.x.contiguous(memory_format=torch.channels_last)  # match the channels-last weights
         step.y = torch.empty(batch, dtype=torch.int64, device=self.device)
         params = list(t.model.parameters())
-        # warm-up (lazy init, cuDNN heuristics) must not change the training state
+        self._make_sinks()
+        if self.grad_flags is None:
+            flags = self.util.shadow_flags() if self.use_shadow else [0] * len(params)
+            self.grad_flags = torch.tensor(flags, dtype=torch.uint8, device=self.device)
+        # warm-up (lazy init, library heuristics) must not change the training state
         saved = (self.flat.clone(), self.momentum_buf.clone(), self.state.clone(), self.acc.clone())
         side = torch.cuda.Stream(device=self.device)
         side.wait_stream(torch.cuda.current_stream(self.device))

@@ -10,7 +10,7 @@ from typing import Any
 import torch
 from torch import nn
 
-from ..ops.bn import bn_act
+from ..ops.bn import bn_act, conv_bn_act
 from .registry import register_model
 
 
@@ -112,9 +112,9 @@ class _BasicBlock(nn.Module):
         self.relu2 = nn.ReLU(inplace=True)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        identity = x if self.downsample is None else bn_act(self.downsample[1], self.downsample[0](x))
-        out = bn_act(self.bn1, self.conv1(x), relu=True)
-        return bn_act(self.bn2, self.conv2(out), relu=True, residual=identity)
+        identity = x if self.downsample is None else conv_bn_act(self.downsample[0], self.downsample[1], x)
+        out = conv_bn_act(self.conv1, self.bn1, x, relu=True)
+        return conv_bn_act(self.conv2, self.bn2, out, relu=True, residual=identity)
 
 
 class ResNet18(nn.Module):
@@ -136,7 +136,7 @@ class ResNet18(nn.Module):
         self.fc = nn.Linear(512, num_classes)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        x = bn_act(self.bn1, self.conv1(x), relu=True)
+        x = conv_bn_act(self.conv1, self.bn1, x, relu=True)
         x = self.layers(x)
         return self.fc(self.flatten(self.pool(x)))
 

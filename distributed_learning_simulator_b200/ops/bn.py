@@ -11,7 +11,7 @@ from torch import nn
 from . import runtime
 
 _DTYPE = {torch.float32: 0, torch.bfloat16: 1}
-STATS = {"fused_fwd": 0, "fallback": 0}
+STATS = {"fused_fwd": 0, "fused_stats": 0, "fallback": 0}
 
 
 def _enabled() -> bool:
@@ -43,17 +43,24 @@ def _scratch(rows: int, channels: int, dtype: int, device: torch.device) -> torc
 
 class _FusedBNAct(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, residual, eps, relu, bn):
+    def forward(ctx, x, weight, bias, residual, eps, relu, bn, stats=None):
         n, c, h, w = x.shape
         rows = n * h * w
         dtype = _DTYPE[x.dtype]
         y = torch.empty_like(x)  # preserves channels-last
         mean = torch.empty(c, dtype=torch.float32, device=x.device)
         invstd = torch.empty(c, dtype=torch.float32, device=x.device)
-        scratch = _scratch(rows, c, dtype, x.device)
-        runtime.call("dls_bn_fwd", x.data_ptr(), dtype, rows, c, weight.data_ptr(), bias.data_ptr(),
-                     runtime.ptr(residual), float(eps), int(relu), y.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
-                     runtime.ptr(scratch), runtime.stream_ptr(x.device))
+        if stats is not None:
+            # the convolution that produced x left sum / sum of squares per channel in its epilogue
+            runtime.call("dls_bn_fwd_stats", x.data_ptr(), dtype, rows, c, weight.data_ptr(), bias.data_ptr(),
+                         runtime.ptr(residual), float(eps), int(relu), y.data_ptr(), mean.data_ptr(),
+                         invstd.data_ptr(), stats.data_ptr(), runtime.stream_ptr(x.device))
+            STATS["fused_stats"] += 1
+        else:
+            scratch = _scratch(rows, c, dtype, x.device)
+            runtime.call("dls_bn_fwd", x.data_ptr(), dtype, rows, c, weight.data_ptr(), bias.data_ptr(),
+                         runtime.ptr(residual), float(eps), int(relu), y.data_ptr(), mean.data_ptr(),
+                         invstd.data_ptr(), runtime.ptr(scratch), runtime.stream_ptr(x.device))
         STATS["fused_fwd"] += 1
         ctx.save_for_backward(x, y if relu else x, weight, mean, invstd)
         ctx.relu, ctx.has_residual, ctx.bn = bool(relu), residual is not None, bn
@@ -75,13 +82,17 @@ class _FusedBNAct(torch.autograd.Function):
         runtime.call("dls_bn_bwd", dy.data_ptr(), y.data_ptr(), x.data_ptr(), dtype, rows, c, weight.data_ptr(),
                      mean.data_ptr(), invstd.data_ptr(), int(ctx.relu), dx.data_ptr(), runtime.ptr(dres),
                      dgamma.data_ptr(), dbeta.data_ptr(), runtime.ptr(scratch), runtime.stream_ptr(x.device))
-        return dx, dgamma, dbeta, dres, None, None, None
+        return dx, dgamma, dbeta, dres, None, None, None, None
 
 
-def bn_act(bn: nn.Module, x: torch.Tensor, relu: bool = False, residual: torch.Tensor | None = None) -> torch.Tensor:
-    """``relu(bn(x) + residual)`` with batch statistics."""
+def bn_act(bn: nn.Module, x: torch.Tensor, relu: bool = False, residual: torch.Tensor | None = None,
+           stats: torch.Tensor | None = None) -> torch.Tensor:
+    """``relu(bn(x) + residual)`` with batch statistics.  ``stats`` ([2, C] fp32: per-channel sum and sum of
+    squares of ``x``, e.g. from the epilogue of the convolution that produced it) skips the reduction pass."""
     if can_fuse(bn, x, residual):
-        return _FusedBNAct.apply(x, bn.weight, bn.bias, residual, bn.eps, relu, bn)
+        if stats is not None and (x.shape[1] // (8 if x.dtype == torch.bfloat16 and x.shape[1] % 8 == 0 else 4)) > 512:
+            stats = None
+        return _FusedBNAct.apply(x, bn.weight, bn.bias, residual, bn.eps, relu, bn, stats)
     STATS["fallback"] += 1
     out = bn(x)
     if residual is not None:
@@ -98,3 +109,16 @@ def oracle_bn_act(x, weight, bias, eps, relu, residual=None):
     if residual is not None:
         out = out + residual.float()
     return torch.relu(out) if relu else out
+
+
+def conv_bn_act(conv: nn.Module, bn: nn.Module, x: torch.Tensor, relu: bool = False,
+                residual: torch.Tensor | None = None) -> torch.Tensor:
+    """``relu(bn(conv(x)) + residual)``: on the tensor-core convolution path the BatchNorm statistics come out
+    of the convolution's epilogue, so the normalisation is a single elementwise launch."""
+    from . import conv as conv_ops
+
+    if getattr(conv, "_dls_own_conv", False) and os.environ.get("DLS_CONV_BN_STATS", "1") != "0" \
+            and not (bn.track_running_stats or bn.running_mean is not None):
+        y, stats = conv_ops.forward_with_stats(conv, x, want_stats=True)
+        return bn_act(bn, y, relu=relu, residual=residual, stats=stats)
+    return bn_act(bn, conv(x), relu=relu, residual=residual)

@@ -54,9 +54,20 @@ _SIGNATURES = {
     "dls_copy_device": [c_void_p, c_void_p, c_ll, c_void_p],
     "dls_gemm_bf16_tn": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                          c_void_p],
+    "dls_conv_supported": [c_void_p],
+    "dls_conv_fprop": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+    "dls_conv_dgrad": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+    "dls_conv_wgrad": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p],
+    "dls_conv_direct_fprop": [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p],
+    "dls_conv_direct_dgrad": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+    "dls_conv_direct_wgrad": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+    "dls_conv_stem_im2col": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p],
+    "dls_tensor_map_probe": [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p],
     "dls_bn_scratch_floats": [c_ll, c_int, c_int],
     "dls_bn_fwd": [c_void_p, c_int, c_ll, c_int, c_void_p, c_void_p, c_void_p, c_float, c_int, c_void_p, c_void_p,
                    c_void_p, c_void_p, c_void_p],
+    "dls_bn_fwd_stats": [c_void_p, c_int, c_ll, c_int, c_void_p, c_void_p, c_void_p, c_float, c_int, c_void_p, c_void_p,
+                         c_void_p, c_void_p, c_void_p],
     "dls_bn_bwd": [c_void_p, c_void_p, c_void_p, c_int, c_ll, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p,
                    c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
     "dls_sign_pack": [c_void_p, c_ll, c_void_p, c_void_p],

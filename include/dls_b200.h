@@ -109,6 +109,11 @@ int dls_bn_scratch_floats(long long rows, int channels, int dtype);
 int dls_bn_fwd(const void* x, int dtype, long long rows, int channels, const float* gamma, const float* beta,
                const void* residual, float eps, int relu, void* y, float* mean, float* invstd, float* scratch,
                void* stream);
+/* Forward when the producing convolution accumulated stats = [2][channels] (sum, sum of squares of x) in its
+ * epilogue (dls_conv_fprop): no reduction launch, one elementwise launch. */
+int dls_bn_fwd_stats(const void* x, int dtype, long long rows, int channels, const float* gamma, const float* beta,
+                     const void* residual, float eps, int relu, void* y, float* mean, float* invstd,
+                     const float* stats, void* stream);
 int dls_bn_bwd(const void* dy, const void* y, const void* x, int dtype, long long rows, int channels,
                const float* gamma, const float* mean, const float* invstd, int relu, void* dx, void* dresidual,
                float* dgamma, float* dbeta, float* scratch, void* stream);
@@ -122,6 +127,53 @@ int dls_bn_bwd(const void* dy, const void* y, const void* x, int dtype, long lon
  * zero-filled by TMA.  b_shared = 1: every batch entry uses the same b and bias. */
 int dls_gemm_bf16_tn(const void* a, const void* b, const float* bias, void* c, int out_dtype, int m, int n, int k,
                      int batch, int b_shared, int relu, void* stream);
+
+/* ---- convolutions (reference: every nn.Conv2d of every local step and server evaluation runs
+ *      in cuDNN inside the external Trainer / Inferencer, simulation_lib/worker/worker.py:86-88,
+ *      server/server.py:40-55) -----------------------------------------------------------------
+ * Tensor-core path (csrc/conv_tc.cu): implicit GEMM on tcgen05, one TMA box load per filter tap.
+ * x [n][h][w][x_pitch] bf16 (c_in channels used), filters [c_out][r][s][c_in] bf16 (the
+ * channels-last arena segment), y [n][oh][ow][y_pitch] bf16; *_pitch = 0 means dense.  c_in, c_out
+ * and pitches % 8 == 0, stride 1 or 2 (stride 2: even h, w and c_in % 64 == 0), dilation 1, groups 1.
+ * dls_conv_supported() tells whether a shape is eligible (else use the dls_conv_direct_* kernels). */
+typedef struct DlsConvShape {
+    int n, h, w, c_in, c_out, r, s, stride, pad_h, pad_w, x_pitch, y_pitch;
+    int dw_pitch, dw_cols; /* wgrad only: elements per (c_out, tap) row of dw and how many of the c_in
+                              columns are written (0 = dense / all): lets a channel-padded input feed an
+                              unpadded gradient */
+} DlsConvShape;
+int dls_conv_supported(const DlsConvShape* shape);
+/* y = conv(x, w) + bias; stats (fp32 [2][c_out], caller-zeroed, may be NULL) receives the per-channel
+ * sum and sum of squares of the stored outputs: the statistics of the BatchNorm that follows. */
+int dls_conv_fprop(const void* x, const void* w, void* y, const float* bias, float* stats,
+                   const DlsConvShape* shape, void* stream);
+/* dx = conv_transpose(dy, w): every element of dx is written (stride-2 parity classes without a tap
+ * get zeros). */
+int dls_conv_dgrad(const void* dy, const void* w, void* dx, const DlsConvShape* shape, void* stream);
+/* dw [c_out][r][s][c_in] fp32.  zeroed != 0: dw holds zeros (or a running sum) and the kernel may
+ * split the pixel range over CTAs, adding partial tiles with vector reductions; zeroed == 0: every
+ * element is stored exactly once (no split). */
+int dls_conv_wgrad(const void* dy, const void* x, float* dw, const DlsConvShape* shape, int zeroed, void* stream);
+/* Direct (CUDA-core) convolutions for layers the tensor-core path does not take: few channels
+ * (the 3-channel stem, LeNet-5's 1/6/16-channel 5x5 layers), any stride / padding.  Every tensor is
+ * addressed through element strides {n, c, h, w} ({o, c, r, s} for filters), dtype 0 = fp32,
+ * 1 = bf16 per operand; accumulation is fp32.  wgrad adds into fp32 dw / dbias (caller-zeroed). */
+typedef struct DlsDirectConv {
+    int n, c_in, h, w, c_out, r, s, oh, ow, stride_h, stride_w, pad_h, pad_w;
+    long long xs[4], ws[4], ys[4];
+    int x_dtype, w_dtype, y_dtype;
+} DlsDirectConv;
+int dls_conv_direct_fprop(const void* x, const void* w, const void* bias, int bias_dtype, void* y,
+                          const DlsDirectConv* d, void* stream);
+int dls_conv_direct_dgrad(const void* dy, const void* w, void* dx, const DlsDirectConv* d, void* stream);
+int dls_conv_direct_wgrad(const void* dy, const void* x, float* dw, float* dbias, const DlsDirectConv* d,
+                          void* stream);
+/* Stem layers (c_in < 8): patches [n * oh * ow][k_pad] bf16 with k = (r * S + s) * c_in + c, zero padded to
+ * k_pad (a multiple of 8), plus the filter re-packed the same way as [c_out][k_pad]; the layer then runs as a
+ * 1x1 convolution over k_pad channels on the tensor-core kernels above.  x / w are addressed through element
+ * strides like the direct kernels (DlsDirectConv: ys unused). */
+int dls_conv_stem_im2col(const void* x, const void* w, void* patches, void* w_packed, int k_pad,
+                         const DlsDirectConv* d, void* stream);
 
 /* ---- quantizers (reference: topology/quantized_endpoint.py:76,82,89,102-104 and the
  *      external cyy_torch_algorithm.quantization; oracle in algorithm/quantization) ---- */
