@@ -39,12 +39,14 @@ if __name__ == "__main__":
 """
 
 
-def run(args, train_per_worker: int, test_per_worker: int, batch: int) -> dict:
+def run(args, conf: dict, samples_per_round: int, meta: dict) -> dict:
+    """``conf``: the flat config dict (written as YAML for ``load_config_from_file``); ``samples_per_round``:
+    training samples all workers consume per round; ``meta``: metric / config description for the JSON line."""
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     result: dict = {}
     if rank == 0:
-        result = _run_rank0(args, train_per_worker, test_per_worker, batch)
+        result = _run_rank0(args, conf, samples_per_round, meta)
     if world > 1:
         import torch.distributed as dist
 
@@ -54,7 +56,7 @@ def run(args, train_per_worker: int, test_per_worker: int, batch: int) -> dict:
     return result
 
 
-def _run_rank0(args, train_per_worker: int, test_per_worker: int, batch: int) -> dict:
+def _run_rank0(args, conf: dict, samples_per_round: int, meta: dict) -> dict:
     import yaml
 
     n = args.gpus
@@ -62,13 +64,7 @@ def _run_rank0(args, train_per_worker: int, test_per_worker: int, batch: int) ->
     work = tempfile.mkdtemp(prefix="ref_arm_")
     conf_path = os.path.join(work, "bench.yaml")
     with open(conf_path, "wt", encoding="utf8") as f:
-        yaml.safe_dump({
-            "dataset_name": "CIFAR10", "model_name": "resnet18", "distributed_algorithm": "fed_avg",
-            "optimizer_name": "SGD", "learning_rate_scheduler_name": "CosineAnnealingLR", "worker_number": n,
-            "batch_size": batch, "round": rounds, "epoch": 1, "learning_rate": 0.1, "use_amp": True,
-            "log_level": "WARNING",
-            "dataset_kwargs": {"train_size": train_per_worker * n, "test_size": test_per_worker * n},
-        }, f)
+        yaml.safe_dump(conf, f)
     timing = os.path.join(work, "timing.txt")
     script = os.path.join(work, "run_reference.py")
     with open(script, "wt", encoding="utf8") as f:
@@ -81,27 +77,31 @@ def _run_rank0(args, train_per_worker: int, test_per_worker: int, batch: int) ->
                PYTHONPATH=os.pathsep.join([os.path.join(ROOT, "baseline", "shims"),
                                            os.path.join(ROOT, "baseline", "_ref")]))
     start = time.time()
-    proc = subprocess.run([sys.executable, script], cwd=work, env=env, capture_output=True, text=True,
-                          timeout=int(os.environ.get("REF_TIMEOUT", "1500")))
+    try:
+        proc = subprocess.run([sys.executable, script], cwd=work, env=env, capture_output=True, text=True,
+                              timeout=int(os.environ.get("REF_TIMEOUT", "1500")))
+    except subprocess.TimeoutExpired:
+        return {"impl": "reference", "unavailable": "reference run exceeded REF_TIMEOUT", "exit_code": 1}
     if proc.returncode != 0:
         return {"impl": "reference", "unavailable": ("reference run failed: " + (proc.stderr or proc.stdout)[-300:])
-                .replace("\n", " ")}
+                .replace("\n", " "), "exit_code": 1}
     with open(timing, "rt", encoding="utf8") as f:
         stamps = [float(line) for line in f if line.strip()]
     if len(stamps) < rounds:
-        return {"impl": "reference", "unavailable": f"expected {rounds} round evaluations, saw {len(stamps)}"}
+        return {"impl": "reference", "unavailable": f"expected {rounds} round evaluations, saw {len(stamps)}",
+                "exit_code": 1}
+    # the last `rounds` evaluations are the per-round test passes (an initial-model evaluation may precede them)
+    stamps = stamps[-rounds:]
     seconds = stamps[args.warmup + args.steps - 1] - stamps[args.warmup - 1]
-    samples = train_per_worker * n * args.steps
+    samples = samples_per_round * args.steps
+    config = dict(meta["config"])
+    config["parallelism"] = f"reference process pool: {n} worker process(es) + server"
+    config["timing"] = "host wall clock between per-round server evaluations (multi-process program)"
     return {
-        "metric": "worker samples/sec (fed_avg ResNet-18, CIFAR-10 shape, federated rounds)",
-        "value": samples / seconds, "unit": "samples/s", "n_gpus": n, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": seconds * 1e3 / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "bf16", "data": "synthetic", "impl": "reference", "rounds_per_s": args.steps / seconds,
-        "config": {"model": "resnet18 (CIFAR stem, 11.17M params)", "algorithm": "fed_avg", "workers": n,
-                   "global_batch": batch * n, "seq_len": None, "local_batch": batch, "local_epochs_per_round": 1,
-                   "train_samples_per_worker": train_per_worker, "test_samples": test_per_worker * n,
-                   "parallelism": f"reference process pool: {n} worker process(es) + server",
-                   "timing": "host wall clock between per-round server evaluations (multi-process program)"},
+        "metric": meta["metric"], "value": samples / seconds, "unit": "samples/s", "n_gpus": n, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": seconds * 1e3 / args.steps, "higher_is_better": True,
+        "scaling": meta["scaling"], "vs_baseline": None, "dtype": meta["dtype"], "data": "synthetic",
+        "impl": "reference", "rounds_per_s": args.steps / seconds, "config": config,
         "e2e": {"value": samples / seconds, "unit": "samples/s",
                 "note": "the reference always feeds batches from host memory; same number as value"},
         "total_wall_s": time.time() - start,

@@ -231,7 +231,7 @@ class Inferencer(Executor):
         if self.device.type == "cuda":
             torch.cuda.synchronize(self.device)
         timing = os.environ.get("REF_TIMING_FILE")
-        if timing:
+        if timing and self.hook_config.log_performance_metric:  # round-level evaluations only (not Shapley subsets)
             # the benchmark harness brackets rounds with the completion time of each evaluation
             with open(timing, "at", encoding="utf8") as f:
                 f.write(f"{time.time()}\n")

@@ -107,12 +107,75 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32])
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// Epilogue of one 32-column chunk of an output row (one thread = one pixel row of the tile): bias, rounding to
+// the stored bf16, 128-bit stores, and -- when `stats` is given -- per-channel sum / sum of squares over the
+// warp's 32 rows added to stats[0][c], stats[1][c] (the BatchNorm that follows needs no reduction pass).
+__device__ __forceinline__ void conv_store_chunk(float (&v)[32], bool row_ok, __nv_bfloat16* dst_row, int col0,
+                                                 int n_out, const float* __restrict__ bias, float* __restrict__ stats,
+                                                 int lane) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        if (bias != nullptr && col0 + j < n_out) v[j] += bias[col0 + j];
+        v[j] = __bfloat162float(__float2bfloat16(v[j]));  // statistics and consumers see the value that is stored
+    }
+    if (row_ok) {
+        __nv_bfloat16* dst = dst_row + col0;
+        if (col0 + 32 <= n_out && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                uint4 pk;
+                __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+                for (int e = 0; e < 4; ++e) hh[e] = __floats2bfloat162_rn(v[8 * q + 2 * e], v[8 * q + 2 * e + 1]);
+                reinterpret_cast<uint4*>(dst)[q] = pk;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                if (col0 + j < n_out) dst[j] = __float2bfloat16(v[j]);
+        }
+    }
+    if (stats != nullptr) {
+        // column sums over the warp's 32 rows: butterfly that halves the value count per step, lane l ends
+        // with the totals of column l
+        float s1[32], s2[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            const float x = row_ok ? v[j] : 0.f;
+            s1[j] = x;
+            s2[j] = x * x;
+        }
+#pragma unroll
+        for (int step = 16; step >= 1; step >>= 1) {
+            const bool upper = (lane & step) != 0;
+#pragma unroll
+            for (int j = 0; j < step; ++j) {
+                // keep columns [j + (upper ? step : 0)], send the other half to the partner lane
+                const float keep1 = upper ? s1[j + step] : s1[j];
+                const float send1 = upper ? s1[j] : s1[j + step];
+                const float keep2 = upper ? s2[j + step] : s2[j];
+                const float send2 = upper ? s2[j] : s2[j + step];
+                s1[j] = keep1 + __shfl_xor_sync(0xffffffffu, send1, step);
+                s2[j] = keep2 + __shfl_xor_sync(0xffffffffu, send2, step);
+            }
+        }
+        if (col0 + lane < n_out) {
+            atomicAdd(stats + col0 + lane, s1[0]);
+            atomicAdd(stats + n_out + col0 + lane, s2[0]);
+        }
+    }
+}
+
+template <int kBlockN>
+constexpr int conv_stages() { return kBlockN == 64 ? 6 : 4; }
+
 template <int kBlockN>
 struct __align__(1024) ConvSmem {
-    __nv_bfloat16 a[kGemmStages][kGemmBlockM * kGemmBlockK];
-    __nv_bfloat16 b[kGemmStages][kBlockN * kGemmBlockK];
-    uint64_t full[kGemmStages];
-    uint64_t empty[kGemmStages];
+    static constexpr int kStages = conv_stages<kBlockN>();
+    __nv_bfloat16 a[kStages][kGemmBlockM * kGemmBlockK];
+    __nv_bfloat16 b[kStages][kBlockN * kGemmBlockK];
+    uint64_t full[kStages];
+    uint64_t empty[kStages];
     uint64_t tmem_full[2];
     uint64_t tmem_empty[2];
     uint32_t tmem_base;
@@ -129,6 +192,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     extern __shared__ unsigned char smem_raw[];
     constexpr uint32_t kBytesB = kBlockN * kGemmBlockK * 2;
     constexpr uint32_t kTmemCols = 2 * kBlockN;
+    constexpr int kStages = conv_stages<kBlockN>();
     using Smem = ConvSmem<kBlockN>;
     Smem& sm = *reinterpret_cast<Smem*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
@@ -141,7 +205,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
-        for (int s = 0; s < kGemmStages; ++s) {
+        for (int s = 0; s < kStages; ++s) {
             mbar_init(&sm.full[s], 1);
             mbar_init(&sm.empty[s], 1);
         }
@@ -176,8 +240,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
                 for (int t = 0; t < ntaps; ++t) {
                     const ConvTap tap = p.taps[tap0 + t];
                     for (int cb = 0; cb < cblocks; ++cb, ++it) {
-                        const int s = it % kGemmStages;
-                        const uint32_t phase = (it / kGemmStages) & 1;
+                        const int s = it % kStages;
+                        const uint32_t phase = (it / kStages) & 1;
                         mbar_wait(&sm.empty[s], phase ^ 1);
                         mbar_expect_tx(&sm.full[s], kBytesA + kBytesB);
                         tma_load_5d(sm.a[s], &map_a, &sm.full[s], tap.pw * p.a_cview + cb * kGemmBlockK, w0 + tap.dw,
@@ -208,8 +272,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t tmem_acc = tmem_base + acc * kBlockN;
                 for (int kb = 0; kb < num_kb; ++kb, ++it) {
-                    const int s = it % kGemmStages;
-                    const uint32_t phase = (it / kGemmStages) & 1;
+                    const int s = it % kStages;
+                    const uint32_t phase = (it / kStages) & 1;
                     mbar_wait(&sm.full[s], phase);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     const uint32_t a_addr = smem_u32(sm.a[s]), b_addr = smem_u32(sm.b[s]);
@@ -261,59 +325,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
                 }
                 float v[32];
 #pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    v[j] = __uint_as_float(r[j]);
-                    if (bias != nullptr && col0 + j < p.n_out) v[j] += bias[col0 + j];
-                    // statistics and consumers see the value that is stored
-                    v[j] = __bfloat162float(__float2bfloat16(v[j]));
-                }
-                if (row_ok) {
-                    __nv_bfloat16* dst = dst_row + col0;
-                    if (col0 + 32 <= p.n_out && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
-#pragma unroll
-                        for (int q = 0; q < 4; ++q) {
-                            uint4 pk;
-                            __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&pk);
-#pragma unroll
-                            for (int e = 0; e < 4; ++e)
-                                hh[e] = __floats2bfloat162_rn(v[8 * q + 2 * e], v[8 * q + 2 * e + 1]);
-                            reinterpret_cast<uint4*>(dst)[q] = pk;
-                        }
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            if (col0 + j < p.n_out) dst[j] = __float2bfloat16(v[j]);
-                    }
-                }
-                if (stats != nullptr) {
-                    // column sums over the warp's 32 rows: butterfly that halves the value count per step,
-                    // lane l ends with the totals of column l
-                    float s1[32], s2[32];
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        const float x = row_ok ? v[j] : 0.f;
-                        s1[j] = x;
-                        s2[j] = x * x;
-                    }
-#pragma unroll
-                    for (int step = 16; step >= 1; step >>= 1) {
-                        const bool upper = (lane & step) != 0;
-#pragma unroll
-                        for (int j = 0; j < step; ++j) {
-                            // keep columns [j + (upper ? step : 0)], send the other half to the partner lane
-                            const float keep1 = upper ? s1[j + step] : s1[j];
-                            const float send1 = upper ? s1[j] : s1[j + step];
-                            const float keep2 = upper ? s2[j + step] : s2[j];
-                            const float send2 = upper ? s2[j] : s2[j + step];
-                            s1[j] = keep1 + __shfl_xor_sync(0xffffffffu, send1, step);
-                            s2[j] = keep2 + __shfl_xor_sync(0xffffffffu, send2, step);
-                        }
-                    }
-                    if (col0 + lane < p.n_out) {
-                        atomicAdd(stats + col0 + lane, s1[0]);
-                        atomicAdd(stats + p.n_out + col0 + lane, s2[0]);
-                    }
-                }
+                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+                conv_store_chunk(v, row_ok, dst_row, col0, p.n_out, bias, stats, lane);
             }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             mbar_arrive(&sm.tmem_empty[acc]);
@@ -321,6 +334,222 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
+    }
+}
+
+// ---- split-K variant for layers with few output tiles and a long reduction ---------------------------------
+// (ResNet stages 3 / 4: 4 096 or 1 024 output pixels, K = 9 x 256 .. 9 x 512).  An SM takes in ~46 B/clk from
+// L2, so a lone CTA walking 72 K blocks of one 128 x 64 tile needs ~27 us while most SMs idle.  Here the
+// kSplit CTAs of a thread-block cluster share ONE 128 x 128 tile: CTA r accumulates K blocks
+// [r * per, (r + 1) * per) in its own tensor memory, then the partial tiles are combined by a reduce-scatter
+// through distributed shared memory -- CTA j owns columns [j * 128 / kSplit, +128 / kSplit): every other CTA
+// writes its partial of those columns into CTA j's receive buffer (st.shared::cluster) and arrives on CTA j's
+// mbarrier (release at cluster scope); CTA j adds them to its own partial and runs the normal epilogue for
+// its columns.  One tile per cluster (no persistent loop): these layers have at most ~64 tiles.
+template <int kSplit>
+struct __align__(1024) SplitSmem {
+    static constexpr int kStages = 4;
+    __nv_bfloat16 a[kStages][kGemmBlockM * kGemmBlockK];
+    __nv_bfloat16 b[kStages][128 * kGemmBlockK];
+    float recv[kSplit - 1][128 / kSplit][kGemmBlockM];  // [source slot][column of my slice][tile row]
+    uint64_t full[kStages];
+    uint64_t empty[kStages];
+    uint64_t tmem_full;
+    uint64_t recv_full;
+    uint32_t tmem_base;
+};
+
+__device__ __forceinline__ uint32_t cluster_rank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t smem_addr, uint32_t cta) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(cta));
+    return r;
+}
+
+template <bool kDgrad, int kSplit>
+__global__ void __launch_bounds__(kConvThreads, 1)
+conv_igemm_splitk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                         const __grid_constant__ ConvGemmParams p, __nv_bfloat16* __restrict__ out,
+                         const float* __restrict__ bias, float* __restrict__ stats) {
+    extern __shared__ unsigned char smem_raw[];
+    constexpr int kBlockN = 128;
+    constexpr int kSlice = kBlockN / kSplit;          // columns finalised by one CTA
+    constexpr uint32_t kBytesB = kBlockN * kGemmBlockK * 2;
+    constexpr uint32_t kTmemCols = kBlockN;
+    using Smem = SplitSmem<kSplit>;
+    constexpr int kStages = Smem::kStages;
+    Smem& sm = *reinterpret_cast<Smem*>(
+        (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int crank = (int)cluster_rank();
+    const int cblocks = (p.a_channels + kGemmBlockK - 1) / kGemmBlockK;
+    const int n_tiles = (p.n_out + kBlockN - 1) / kBlockN;
+    const int p_tiles = p.tiles_w * p.tiles_h * p.tiles_n;
+    const int tile = blockIdx.x / kSplit;             // grid = tiles * kSplit exactly
+    const int nt = tile % n_tiles;
+    const int pt = (tile / n_tiles) % p_tiles, cls = (tile / n_tiles) / p_tiles;
+    const int num_kb = p.class_ntaps[cls] * cblocks;
+    const int per = (num_kb + kSplit - 1) / kSplit;
+    const int kb_begin = min(crank * per, num_kb), kb_end = min(kb_begin + per, num_kb);
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(&sm.full[s], 1);
+            mbar_init(&sm.empty[s], 1);
+        }
+        mbar_init(&sm.tmem_full, 1);
+        mbar_init(&sm.recv_full, (kSplit - 1) * 128);  // every epilogue thread of every other CTA
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm.tmem_base)),
+                     "r"(kTmemCols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    // every CTA's receive barrier exists before a peer writes to it
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = sm.tmem_base;
+    const int w0 = (pt % p.tiles_w) * p.bw;
+    const int h0 = ((pt / p.tiles_w) % p.tiles_h) * p.bh;
+    const int n0 = (pt / (p.tiles_w * p.tiles_h)) * p.bn;
+
+    if (warp == 0) {
+        if (lane == 0) {  // ---- TMA producer over this CTA's share of the K blocks
+            const int tap0 = p.class_tap0[cls];
+            uint32_t it = 0;
+            for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
+                const ConvTap tap = p.taps[tap0 + kb / cblocks];
+                const int cb = kb % cblocks;
+                const int s = it % kStages;
+                const uint32_t phase = (it / kStages) & 1;
+                mbar_wait(&sm.empty[s], phase ^ 1);
+                mbar_expect_tx(&sm.full[s], kBytesA + kBytesB);
+                tma_load_5d(sm.a[s], &map_a, &sm.full[s], tap.pw * p.a_cview + cb * kGemmBlockK, w0 + tap.dw, tap.ph,
+                            h0 + tap.dh, n0);
+                if (!kDgrad) {
+                    tma_load_3d(sm.b[s], &map_b, &sm.full[s], cb * kGemmBlockK, tap.widx, nt * kBlockN);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < kBlockN / 64; ++j)
+                        tma_load_3d(reinterpret_cast<unsigned char*>(sm.b[s]) + j * 8192, &map_b, &sm.full[s],
+                                    nt * kBlockN + j * 64, tap.widx, cb * kGemmBlockK);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {  // ---- MMA issuer
+            const uint32_t idesc = conv_instr_desc<kBlockN, false, kDgrad>();
+            uint32_t it = 0;
+            for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
+                const int s = it % kStages;
+                const uint32_t phase = (it / kStages) & 1;
+                mbar_wait(&sm.full[s], phase);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t a_addr = smem_u32(sm.a[s]), b_addr = smem_u32(sm.b[s]);
+#pragma unroll
+                for (int kk = 0; kk < kGemmBlockK / kGemmUmmaK; ++kk) {
+                    const uint64_t da = umma_smem_desc(a_addr + kk * kGemmUmmaK * 2);
+                    const uint64_t db = kDgrad ? umma_smem_desc_mn(b_addr + kk * 2048, 8192)
+                                               : umma_smem_desc(b_addr + kk * kGemmUmmaK * 2);
+                    umma_bf16(tmem_base, da, db, idesc, (kb > kb_begin) || kk != 0);
+                }
+                umma_commit(&sm.empty[s]);
+            }
+            umma_commit(&sm.tmem_full);
+        }
+    } else {
+        // ---- epilogue: reduce-scatter of the partial tiles, then the usual store of my column slice
+        const int quarter = warp & 3;
+        const int m_local = quarter * 32 + lane;
+        const bool has_acc = kb_end > kb_begin;
+        mbar_wait(&sm.tmem_full, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t recv_base = smem_u32(&sm.recv[0][0][0]);
+        const uint32_t recv_bar = smem_u32(&sm.recv_full);
+#pragma unroll 1
+        for (int d = 1; d < kSplit; ++d) {
+            const int dest = (crank + d) % kSplit;
+            const int slot = crank > dest ? crank - 1 : crank;  // my index among dest's kSplit - 1 sources
+            const uint32_t remote = map_to_cta(recv_base, (uint32_t)dest) + (uint32_t)((slot * kSlice) * kGemmBlockM + m_local) * 4u;
+#pragma unroll 1
+            for (int chunk = 0; chunk < kSlice / 32; ++chunk) {
+                uint32_t r[32];
+                if (has_acc) {
+                    tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(dest * kSlice + chunk * 32), r);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) r[j] = 0u;
+                }
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(remote + (uint32_t)((chunk * 32 + j) * kGemmBlockM) * 4u),
+                                 "r"(r[j])
+                                 : "memory");
+            }
+            // release my stores to the destination CTA and count this thread in
+            asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(map_to_cta(recv_bar, (uint32_t)dest))
+                         : "memory");
+        }
+        // my slice: own partial + the kSplit - 1 received ones
+        {
+            uint32_t done = 0;
+            for (uint32_t spins = 0; !done; ++spins) {
+                asm volatile(
+                    "{\n\t.reg .pred p;\n\t"
+                    "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+                    "selp.u32 %0, 1, 0, p;\n\t}"
+                    : "=r"(done)
+                    : "r"(recv_bar), "r"(0u)
+                    : "memory");
+                if (spins > 20000000u) asm volatile("trap;");
+            }
+        }
+        const int lw = m_local % p.bw, lh = (m_local / p.bw) % p.bh, ln = m_local / (p.bw * p.bh);
+        const int w = w0 + lw, h = h0 + lh, n = n0 + ln;
+        const bool row_ok = w < p.pw && h < p.ph && n < p.pn;
+        __nv_bfloat16* dst_row = out +
+            (((long long)n * p.out_h + (h * p.os + p.class_oph[cls])) * p.out_w + (w * p.os + p.class_opw[cls])) *
+                (long long)p.out_pitch;
+#pragma unroll 1
+        for (int chunk = 0; chunk < kSlice / 32; ++chunk) {
+            const int col0 = nt * kBlockN + crank * kSlice + chunk * 32;
+            if (col0 >= p.n_out) break;
+            float v[32];
+            if (has_acc) {
+                uint32_t r[32];
+                tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(crank * kSlice + chunk * 32), r);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = 0.f;
+            }
+#pragma unroll
+            for (int src = 0; src < kSplit - 1; ++src)
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] += sm.recv[src][chunk * 32 + j][m_local];
+            conv_store_chunk(v, row_ok, dst_row, col0, p.n_out, bias, stats, lane);
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    // no CTA leaves while a peer may still write into its receive buffer or arrive on its barrier
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
     if (warp == 1) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
@@ -348,6 +577,7 @@ struct WgradParams {
     int n_taps, taps_total;          // taps handled here / taps of the filter (row pitch of dW)
     int split, tiles_per_split;
     int atomic;
+    int out_bf16;                    // store mode only: dw is bf16
     int dw_pitch, dw_cols;           // elements per (k, tap) row of dw, columns actually written
     ConvTap taps[kConvMaxTaps];
 };
@@ -474,7 +704,9 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_const
             mbar_wait(&sm.tmem_full[acc], use & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t tmem_acc = tmem_base + acc * kBlockN;
-            float* dst_row = dw + ((long long)row * p.taps_total + widx) * p.dw_pitch;
+            const long long row_off = ((long long)row * p.taps_total + widx) * p.dw_pitch;
+            float* dst_row = dw + row_off;
+            __nv_bfloat16* dst_row_h = reinterpret_cast<__nv_bfloat16*>(dw) + row_off;
 #pragma unroll 1
             for (int chunk = 0; chunk < kBlockN / 32; ++chunk) {
                 const int col0 = nt * kBlockN + chunk * 32;
@@ -484,7 +716,25 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_const
                 if (row < p.c_out && has_acc) {
                     float* dst = dst_row + col0;
                     const bool vec = col0 + 32 <= p.dw_cols && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0);
-                    if (p.atomic) {
+                    if (p.out_bf16) {
+                        __nv_bfloat16* dh = dst_row_h + col0;
+                        if (col0 + 32 <= p.dw_cols && ((reinterpret_cast<uintptr_t>(dh) & 15) == 0)) {
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                uint4 pk;
+                                __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+                                for (int e = 0; e < 4; ++e)
+                                    hh[e] = __floats2bfloat162_rn(__uint_as_float(r[8 * q + 2 * e]),
+                                                                  __uint_as_float(r[8 * q + 2 * e + 1]));
+                                reinterpret_cast<uint4*>(dh)[q] = pk;
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (col0 + j < p.dw_cols) dh[j] = __float2bfloat16(__uint_as_float(r[j]));
+                        }
+                    } else if (p.atomic) {
                         if (vec) {
 #pragma unroll
                             for (int q = 0; q < 8; ++q)
@@ -598,12 +848,51 @@ static int set_smem(Kernel kernel, size_t smem) {
     return 0;
 }
 
+template <bool kDgrad, int kSplit>
+static int launch_splitk(const CUtensorMap& map_a, const CUtensorMap& map_b, const ConvGemmParams& p, void* out,
+                         const float* bias, float* stats, long long tiles, cudaStream_t st) {
+    auto kernel = conv_igemm_splitk_kernel<kDgrad, kSplit>;
+    const size_t smem = sizeof(SplitSmem<kSplit>) + 1024;
+    static thread_local bool configured = false;
+    if (!configured) {
+        if (int rc = set_smem(kernel, smem)) return rc;
+        configured = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(tiles * kSplit));
+    cfg.blockDim = dim3(kConvThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = kSplit;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    DLS_CHECK(cudaLaunchKernelEx(&cfg, kernel, map_a, map_b, p, (__nv_bfloat16*)out, bias, stats));
+    return 0;
+}
+
+// split-K factor (0 = use the persistent kernel): only when 128 x 128 tiles leave most SMs idle and every CTA of
+// the cluster still gets a few K blocks
+static int pick_split(int n_out, long long tiles128, int min_kb) {
+    static const int forced = [] { const char* e = getenv("DLS_CONV_SPLITK"); return e ? atoi(e) : -1; }();
+    if (forced == 0) return 0;
+    if (n_out < 128 || n_out % 32) return 0;
+    int split = 0;
+    if (tiles128 * 4 <= kNumSMs + 12 && min_kb >= 8) split = 4;
+    else if (tiles128 * 2 <= kNumSMs + 12 && min_kb >= 4) split = 2;
+    if (forced == 2 || forced == 4) split = (min_kb >= forced) ? forced : split;
+    return split;
+}
+
 static int pick_block_n(int n_out, long long p_tiles) {
     static const int forced = [] { const char* e = getenv("DLS_CONV_BN"); return e ? atoi(e) : 0; }();
     if (forced == 64 || forced == 128) return n_out > 64 ? forced : 64;
     if (n_out <= 64) return 64;
     // wide tiles only when they still give every SM a tile
-    return (p_tiles * ((n_out + 127) / 128) >= kNumSMs) ? 128 : 64;
+    return (p_tiles * ((n_out + 127) / 128) >= 100) ? 128 : 64;
 }
 
 }  // namespace dls
@@ -648,6 +937,18 @@ extern "C" int dls_conv_fprop(const void* x, const void* w, void* y, const float
             t.widx = (uint16_t)(r * cs.s + s);
         }
     const long long p_tiles = (long long)p.tiles_w * p.tiles_h * p.tiles_n;
+    const int cblocks = (cs.c_in + 63) / 64;
+    if (const int split = pick_split(cs.c_out, p_tiles * ((cs.c_out + 127) / 128), cs.r * cs.s * cblocks)) {
+        CUtensorMap ma, mb;
+        if (int rc = make_act_map(&ma, x, cs.n, cs.h, cs.w, cs.c_in, p.a_cview, cs.stride, p.bw, p.bh, p.bn)) return rc;
+        if (int rc = make_filter_map(&mb, w, cs.c_out, cs.r * cs.s, cs.c_in, 128)) return rc;
+        const long long tiles = p_tiles * ((cs.c_out + 127) / 128);
+        const int rc = split == 4 ? launch_splitk<false, 4>(ma, mb, p, y, bias, stats, tiles, (cudaStream_t)stream)
+                                  : launch_splitk<false, 2>(ma, mb, p, y, bias, stats, tiles, (cudaStream_t)stream);
+        if (rc) return rc;
+        DLS_LAUNCHED("conv_igemm_splitk_kernel<fprop>");
+        return 0;
+    }
     const int block_n = pick_block_n(cs.c_out, p_tiles);
     CUtensorMap map_a, map_b;
     if (int rc = make_act_map(&map_a, x, cs.n, cs.h, cs.w, cs.c_in, p.a_cview, cs.stride, p.bw, p.bh, p.bn)) return rc;
@@ -703,6 +1004,20 @@ extern "C" int dls_conv_dgrad(const void* dy, const void* w, void* dx, const Dls
             p.class_ntaps[cls] = n_taps - p.class_tap0[cls];
         }
     const long long p_tiles = (long long)p.tiles_w * p.tiles_h * p.tiles_n * p.n_classes;
+    const int kblocks = (cs.c_out + 63) / 64;
+    int min_kb = 1 << 30;
+    for (int c = 0; c < p.n_classes; ++c) min_kb = p.class_ntaps[c] * kblocks < min_kb ? p.class_ntaps[c] * kblocks : min_kb;
+    if (const int split = pick_split(cs.c_in, p_tiles * ((cs.c_in + 127) / 128), min_kb)) {
+        CUtensorMap ma, mb;
+        if (int rc = make_act_map(&ma, dy, cs.n, oh, ow, cs.c_out, p.a_cview, 1, p.bw, p.bh, p.bn)) return rc;
+        if (int rc = make_filter_map(&mb, w, cs.c_out, cs.r * cs.s, cs.c_in, 64)) return rc;
+        const long long tiles = p_tiles * ((cs.c_in + 127) / 128);
+        const int rc = split == 4 ? launch_splitk<true, 4>(ma, mb, p, dx, nullptr, nullptr, tiles, (cudaStream_t)stream)
+                                  : launch_splitk<true, 2>(ma, mb, p, dx, nullptr, nullptr, tiles, (cudaStream_t)stream);
+        if (rc) return rc;
+        DLS_LAUNCHED("conv_igemm_splitk_kernel<dgrad>");
+        return 0;
+    }
     const int block_n = pick_block_n(cs.c_in, p_tiles);
     CUtensorMap map_a, map_b;
     if (int rc = make_act_map(&map_a, dy, cs.n, oh, ow, cs.c_out, p.a_cview, 1, p.bw, p.bh, p.bn)) return rc;
@@ -728,8 +1043,12 @@ extern "C" int dls_conv_dgrad(const void* dy, const void* w, void* dx, const Dls
     return 0;
 }
 
-extern "C" int dls_conv_wgrad(const void* dy, const void* x, float* dw, const DlsConvShape* shape, int zeroed,
+extern "C" int dls_conv_wgrad(const void* dy, const void* x, void* dw_out, const DlsConvShape* shape, int mode,
                               void* stream) {
+    // mode 0: store fp32, 1: accumulate into fp32 (may split the pixel range), 2: store bf16
+    if (mode < 0 || mode > 2) return fail_msg("dls_conv_wgrad: mode must be 0, 1 or 2");
+    float* dw = reinterpret_cast<float*>(dw_out);
+    const int zeroed = mode == 1;
     const DlsConvShape cs = *shape;
     if (int rc = check_conv(cs, "wgrad")) return rc;
     if (((uintptr_t)dy | (uintptr_t)x | (uintptr_t)dw) & 15) return fail_msg("dls_conv_wgrad: operands must be 16-byte aligned");
@@ -764,6 +1083,7 @@ extern "C" int dls_conv_wgrad(const void* dy, const void* x, float* dw, const Dl
     split = (p_tiles + p.tiles_per_split - 1) / p.tiles_per_split;
     p.split = split;
     p.atomic = zeroed ? 1 : 0;  // accumulate mode always adds (dw may hold a running sum)
+    p.out_bf16 = mode == 2 ? 1 : 0;
     CUtensorMap map_dy, map_x;
     if (int rc = make_act_map(&map_dy, dy, cs.n, oh, ow, cs.c_out, cs.y_pitch ? cs.y_pitch : cs.c_out, 1, p.bw, p.bh, p.bn))
         return rc;

@@ -140,9 +140,8 @@ class GraphTrainStep:
                 w = module.weight
                 if not w.requires_grad:
                     continue
-                # [buffer, accumulate?]: the second entry is decided by the layer's first forward (whether
-                # its weight-gradient kernel splits the pixel range and adds partial tiles)
-                entry = [torch.zeros_like(w, dtype=torch.float32), None]
+                # [buffer, accumulate?]: both are decided by the layer's first forward (ops/conv.py)
+                entry = [None, None]
                 self.wgrad_sinks[id(module)] = entry
                 self._sink_of_param[id(w)] = entry
 
@@ -152,12 +151,15 @@ class GraphTrainStep:
         ptrs, flags = [], []
         base_flags = self.util.shadow_flags() if self.use_shadow else [0] * len(params)
         for p, g, f in zip(params, step.grads, base_flags):
-            if g is None and id(p) in self._sink_of_param:
+            if g is None and id(p) in self._sink_of_param and self._sink_of_param[id(p)][0] is not None:
                 # the convolution wrote its weight gradient into the sink (fp32, accumulating): bit 2 lets
                 # the update clear it for the next step; bit 1 keeps the bf16 shadow rewrite
                 sink, accumulate = self._sink_of_param[id(p)]
                 ptrs.append(sink.data_ptr())
-                flags.append((2 if f else 0) | (4 if accumulate else 0))
+                if sink.dtype == torch.bfloat16:
+                    flags.append(1)  # stored once per step in the shadow's dtype: an ordinary bf16 gradient
+                else:
+                    flags.append((2 if f else 0) | (4 if accumulate else 0))
                 continue
             # the fused update walks physical memory: a gradient must be laid out like its parameter
             # (autograd's layout contract gives channels-last grads for channels-last weights)

@@ -136,12 +136,15 @@ def tc_dgrad(dy: torch.Tensor, weight: torch.Tensor, shape: DlsConvShape) -> tor
 
 def tc_wgrad(dy: torch.Tensor, x: torch.Tensor, shape: DlsConvShape, out: torch.Tensor | None = None,
              accumulate: bool = True) -> torch.Tensor:
-    """fp32 ``[Cout, Cin, R, S]`` in channels-last physical order.  ``accumulate``: ``out`` holds zeros (or a
-    running sum) and the kernel may split the pixel range; otherwise every element is stored once."""
+    """``[Cout, Cin, R, S]`` in channels-last physical order.  ``accumulate``: ``out`` (fp32) holds zeros or a
+    running sum and the kernel may split the pixel range; otherwise every element is stored once, in the dtype of
+    ``out`` (fp32 or bf16)."""
     if out is None:
         out = torch.zeros((shape.c_out, shape.r, shape.s, shape.c_in), dtype=torch.float32,
                           device=dy.device).permute(0, 3, 1, 2)
-    runtime.call("dls_conv_wgrad", dy.data_ptr(), x.data_ptr(), out.data_ptr(), ctypes.byref(shape), int(accumulate),
+    assert out.dtype == torch.float32 or not accumulate
+    mode = 1 if accumulate else (2 if out.dtype == torch.bfloat16 else 0)
+    runtime.call("dls_conv_wgrad", dy.data_ptr(), x.data_ptr(), out.data_ptr(), ctypes.byref(shape), mode,
                  runtime.stream_ptr(dy.device))
     return out
 
@@ -178,6 +181,7 @@ class _Conv2d(torch.autograd.Function):
     @staticmethod
     def forward(ctx: Any, x: torch.Tensor, weight: torch.Tensor, bias: Any, stride: tuple, padding: tuple, mode: int,
                 compute_dtype: torch.dtype, side: Any, sink: Any, sink_zeroed: bool, want_stats: bool) -> tuple:
+        ctx.set_materialize_grads(False)  # no zero-filled gradient tensor for the statistics output
         ctx.conf = (stride, padding, mode, compute_dtype)
         ctx.side, ctx.sink, ctx.sink_zeroed = side, sink, sink_zeroed
         ctx.has_bias = bias is not None
@@ -227,6 +231,8 @@ class _Conv2d(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx: Any, dy: torch.Tensor, _dstats: Any = None) -> tuple:
+        if dy is None:
+            return (None,) * 11
         x, weight = ctx.saved_tensors  # mode 3: x holds the patch matrix
         stride, padding, mode, compute_dtype = ctx.conf
         side, sink = ctx.side, ctx.sink
@@ -334,9 +340,13 @@ def forward_with_stats(self: nn.Conv2d, x: torch.Tensor, want_stats: bool = True
     if sinks is not None and torch.is_grad_enabled():
         entry = sinks.get(id(self))
         if entry is not None:
-            if entry[1] is None:
-                entry[1] = mode != 1 or wgrad_needs_zero(
-                    tc_shape(tuple(x.shape), tuple(self.weight.shape), self.stride, self.padding))
+            if entry[0] is None:
+                # first forward of the layer inside a training step: decide whether its weight-gradient kernel
+                # splits the pixel range (fp32 sink that accumulates) or stores once (sink in the filter's dtype)
+                w = self.weight
+                entry[1] = mode != 1 or wgrad_needs_zero(tc_shape(tuple(x.shape), tuple(w.shape), self.stride, self.padding))
+                keep = torch.bfloat16 if (not entry[1] and w.dtype == torch.bfloat16) else torch.float32
+                entry[0] = torch.zeros_like(w, dtype=keep)
             sink, zeroed = entry
     return _Conv2d.apply(x, self.weight, self.bias, tuple(self.stride), tuple(self.padding), mode, dtype, side, sink,
                          bool(zeroed), want_stats)

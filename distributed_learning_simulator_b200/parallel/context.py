@@ -138,6 +138,9 @@ class ArenaPayload(dict):
 
 class DistributedContext:
     def __init__(self) -> None:
+        self._agg_checks_left = int(os.environ.get("DLS_AGG_CHECK", "0"))
+        self.agg_max_abs_err = 0.0
+        self.agg_checks_done = 0
         self.rank = int(os.environ.get("RANK", "0"))
         self.world = int(os.environ.get("WORLD_SIZE", "1"))
         self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -269,6 +272,21 @@ class DistributedContext:
                          float(old_scale), float(inv_total), dsts, self.world, lo, hi, self._flag_table.data_ptr(),
                          self.world, self.rank, self.epoch, self._nan.data_ptr(), runtime.stream_ptr(self.device))
         self.p2p_reductions += 1
+        if self._agg_checks_left > 0:
+            # self-check (bench warm-up rounds, DLS_AGG_CHECK=<calls>): the same reduction as an fp64 NCCL
+            # all-reduce of every rank's locally weighted rows
+            self._agg_checks_left -= 1
+            acc = torch.zeros(n, dtype=torch.float64, device=self.device)
+            for payload, wt in zip(payloads, weights):
+                if payload.rank == self.rank and payload.local is not None:
+                    acc.add_(payload.local.double(), alpha=float(wt))
+            dist.all_reduce(acc)
+            acc.mul_(float(inv_total))
+            if old is not None:
+                acc.add_(old.double(), alpha=float(old_scale))
+            got = self.globals.local_tensor(torch.float32, n, off).double()
+            self.agg_max_abs_err = max(self.agg_max_abs_err, float((got - acc).abs().max().item()))
+            self.agg_checks_done += 1
         verdict = self.flags.local_tensor(torch.int32, 32)[16:25].cpu().tolist()
         if verdict[8]:
             raise RuntimeError("peer barrier timed out inside fedavg_reduce (a rank is missing)")

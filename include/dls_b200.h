@@ -150,10 +150,10 @@ int dls_conv_fprop(const void* x, const void* w, void* y, const float* bias, flo
 /* dx = conv_transpose(dy, w): every element of dx is written (stride-2 parity classes without a tap
  * get zeros). */
 int dls_conv_dgrad(const void* dy, const void* w, void* dx, const DlsConvShape* shape, void* stream);
-/* dw [c_out][r][s][c_in] fp32.  zeroed != 0: dw holds zeros (or a running sum) and the kernel may
- * split the pixel range over CTAs, adding partial tiles with vector reductions; zeroed == 0: every
- * element is stored exactly once (no split). */
-int dls_conv_wgrad(const void* dy, const void* x, float* dw, const DlsConvShape* shape, int zeroed, void* stream);
+/* dw [c_out][r][s][c_in].  mode 1: dw is fp32 and holds zeros (or a running sum); the kernel may split the
+ * pixel range over CTAs and adds its partial tiles with vector reductions.  mode 0 / 2: every element is stored
+ * exactly once (no split), as fp32 / as bf16. */
+int dls_conv_wgrad(const void* dy, const void* x, void* dw, const DlsConvShape* shape, int mode, void* stream);
 /* Direct (CUDA-core) convolutions for layers the tensor-core path does not take: few channels
  * (the 3-channel stem, LeNet-5's 1/6/16-channel 5x5 layers), any stride / padding.  Every tensor is
  * addressed through element strides {n, c, h, w} ({o, c, r, s} for filters), dtype 0 = fp32,

@@ -73,7 +73,11 @@ def test_wgrad(case):
     _close(dw, dw_ref, case[0] * case[2] * case[3])
     dw2 = torch.full_like(dw, 3.0)  # store mode overwrites whatever is there
     C.tc_wgrad(dy, x, shape, out=dw2, accumulate=False)
-    _close(dw2, dw_ref, case[0] * case[2] * case[3])
+    # one CTA walks the whole pixel range in store mode: a single fp32 chain of up to 1.3 M products
+    torch.testing.assert_close(dw2, dw_ref, rtol=0, atol=float(dw_ref.abs().max()) * (1e-4 + 2e-6 * (case[0] * case[2] * case[3]) ** 0.5))
+    dwh = torch.full_like(dw, 3.0).bfloat16()  # the same, stored as bf16 (gradient sinks of non-split layers)
+    C.tc_wgrad(dy, x, shape, out=dwh, accumulate=False)
+    torch.testing.assert_close(dwh.float(), dw_ref, rtol=0, atol=float(dw_ref.abs().max()) * (8e-3 + 2e-6 * (case[0] * case[2] * case[3]) ** 0.5))
     C.tc_wgrad(dy, x, shape, out=dw, accumulate=True)  # a second pass adds
     _close(dw, 2 * dw_ref, case[0] * case[2] * case[3])
 
