@@ -168,6 +168,8 @@ __global__ void __launch_bounds__(kBnThreads)
 bn_fwd_kernel(const T* __restrict__ x, const T* __restrict__ residual, long long rows, int channels,
               const float* __restrict__ gamma, const float* __restrict__ beta, float eps, int relu, int w,
               int cached, T* __restrict__ y, float* __restrict__ mean, float* __restrict__ invstd) {
+    pdl_launch_dependents();
+    pdl_wait();
     using Raw = typename RawVec<T, V>::type;
     extern __shared__ __align__(16) unsigned char s_dyn[];
     Raw* s_x = reinterpret_cast<Raw*>(s_dyn);
@@ -238,6 +240,8 @@ bn_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* __rest
               int channels, const float* __restrict__ gamma, const float* __restrict__ mean,
               const float* __restrict__ invstd, int relu, int w, int cached, T* __restrict__ dx,
               T* __restrict__ dresidual, float* __restrict__ dgamma, float* __restrict__ dbeta) {
+    pdl_launch_dependents();
+    pdl_wait();
     using Raw = typename RawVec<T, V>::type;
     extern __shared__ __align__(16) unsigned char s_dyn[];
     Raw* s_g = reinterpret_cast<Raw*>(s_dyn);   // masked upstream gradient, then x, per thread slot
@@ -353,6 +357,8 @@ __global__ void __launch_bounds__(kWideThreads)
 bn_wide_reduce_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T* __restrict__ y, long long rows,
                       int channels, const float* __restrict__ mean, const float* __restrict__ invstd, int relu,
                       float* __restrict__ partials) {
+    pdl_launch_dependents();
+    pdl_wait();
     extern __shared__ __align__(16) float s_wide[];
     float* s_buf = s_wide;                              // [kWideThreads][2V]
     float* s_part = s_wide + kWideThreads * 2 * V;      // [2][channels]
@@ -413,6 +419,8 @@ bn_wide_apply_kernel(const T* __restrict__ x, const T* __restrict__ aux, const T
                      float eps, int relu, const float* __restrict__ partials, int n_partials,
                      float* __restrict__ mean, float* __restrict__ invstd, float* __restrict__ dgamma,
                      float* __restrict__ dbeta, T* __restrict__ out, T* __restrict__ dresidual) {
+    pdl_launch_dependents();
+    pdl_wait();
     // forward : x = input, y_or_res = residual (may be null), out = y; writes mean / invstd
     // backward: x = input, aux = dy, y_or_res = forward output (ReLU mask), out = dx; reads mean /
     //           invstd, writes dgamma / dbeta
@@ -517,13 +525,15 @@ static cudaError_t wide_launch(K kernel, int grid, int cluster, size_t smem, cud
     cfg.blockDim = dim3(kWideThreads);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = (unsigned)cluster;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = pdl_enabled() ? 2 : 1;
     return cudaLaunchKernelEx(&cfg, kernel, args...);
 }
 
@@ -610,13 +620,15 @@ static cudaError_t bn_launch(K kernel, const BnPlan& p, size_t dyn_smem, cudaStr
     cfg.gridDim = dim3((unsigned)(p.groups * p.cluster));
     cfg.blockDim = dim3(kBnThreads);
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = (unsigned)p.cluster;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = pdl_enabled() ? 2 : 1;
     return cudaLaunchKernelEx(&cfg, kernel, args...);
 }
 

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include <atomic>
 
@@ -35,6 +36,49 @@ inline int fail_msg(const char* what) {
     } while (0)
 
 constexpr int kNumSMs = 148;  // B200
+
+// ---- programmatic dependent launch ---------------------------------------------------------------
+// Inside the captured training step ~150 small kernels run back to back; the gap between two dependent
+// kernels (drain, launch, prologue) is a visible share of the step.  Kernels launched through launch_pdl()
+// may start while their predecessor in the stream is still running: every CTA first lets ITS successor
+// launch (pdl_launch_dependents), does the work that does not touch the predecessor's data (barrier
+// init, tensor-memory allocation, descriptor prefetch, index maths) and only then waits for the
+// predecessor grid to complete and flush (pdl_wait).  Without the launch attribute both are no-ops.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+inline bool pdl_enabled() {
+    static const bool on = [] { const char* e = getenv("DLS_PDL"); return e == nullptr || e[0] != '0'; }();
+    return on;
+}
+
+// cluster == 0: no cluster attribute
+template <typename K, typename... Args>
+inline cudaError_t launch_pdl(K kernel, dim3 grid, dim3 block, size_t smem, cudaStream_t stream, int cluster,
+                              Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[2];
+    int n = 0;
+    if (cluster > 0) {
+        attr[n].id = cudaLaunchAttributeClusterDimension;
+        attr[n].val.clusterDim.x = (unsigned)cluster;
+        attr[n].val.clusterDim.y = 1;
+        attr[n].val.clusterDim.z = 1;
+        ++n;
+    }
+    if (pdl_enabled()) {
+        attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[n].val.programmaticStreamSerializationAllowed = 1;
+        ++n;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = n;
+    return cudaLaunchKernelEx(&cfg, kernel, args...);
+}
 
 inline int grid_for(long long work_items, int threads, int blocks_per_sm) {
     long long blocks = (work_items + threads - 1) / threads;

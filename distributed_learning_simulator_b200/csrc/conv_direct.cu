@@ -205,6 +205,8 @@ conv_direct_wgrad_kernel(const void* __restrict__ dy, const void* __restrict__ x
 __global__ void __launch_bounds__(kDirectThreads)
 conv_stem_im2col_kernel(const void* __restrict__ x, const void* __restrict__ w, __nv_bfloat16* __restrict__ patches,
                         __nv_bfloat16* __restrict__ w_packed, int k_pad, const __grid_constant__ DlsDirectConv d) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int q_count = d.c_in * d.r * d.s;
     const int groups = k_pad / 8;
     const long long pixels = (long long)d.n * d.oh * d.ow;
@@ -311,8 +313,8 @@ extern "C" int dls_conv_stem_im2col(const void* x, const void* w, void* patches,
     const long long w_work = (long long)d->c_out * k_pad;
     if (w_work > work) work = w_work;
     const long long blocks = (work + kDirectThreads - 1) / kDirectThreads;
-    conv_stem_im2col_kernel<<<(unsigned)blocks, kDirectThreads, 0, (cudaStream_t)stream>>>(
-        x, w, (__nv_bfloat16*)patches, (__nv_bfloat16*)w_packed, k_pad, *d);
+    DLS_CHECK(launch_pdl(conv_stem_im2col_kernel, dim3((unsigned)blocks), dim3(kDirectThreads), 0, (cudaStream_t)stream, 0,
+                         x, w, (__nv_bfloat16*)patches, (__nv_bfloat16*)w_packed, k_pad, *d));
     DLS_LAUNCHED("conv_stem_im2col_kernel");
     return 0;
 }

@@ -197,6 +197,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     Smem& sm = *reinterpret_cast<Smem*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    pdl_launch_dependents();
     const int cblocks = (p.a_channels + kGemmBlockK - 1) / kGemmBlockK;
     const int n_tiles = (p.n_out + kBlockN - 1) / kBlockN;
     const int p_tiles = p.tiles_w * p.tiles_h * p.tiles_n;
@@ -225,6 +226,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = sm.tmem_base;
+    pdl_wait();  // everything above is independent of the previous kernel's output
 
     if (warp == 0) {
         if (lane == 0) {  // ---- TMA producer
@@ -388,6 +390,7 @@ conv_igemm_splitk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
     Smem& sm = *reinterpret_cast<Smem*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    pdl_launch_dependents();
     const int crank = (int)cluster_rank();
     const int cblocks = (p.a_channels + kGemmBlockK - 1) / kGemmBlockK;
     const int n_tiles = (p.n_out + kBlockN - 1) / kBlockN;
@@ -423,6 +426,7 @@ conv_igemm_splitk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = sm.tmem_base;
+    pdl_wait();  // everything above is independent of the previous kernel's output
     const int w0 = (pt % p.tiles_w) * p.bw;
     const int h0 = ((pt / p.tiles_w) % p.tiles_h) * p.bh;
     const int n0 = (pt / (p.tiles_w * p.tiles_h)) * p.bn;
@@ -594,6 +598,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_const
     Smem& sm = *reinterpret_cast<Smem*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    pdl_launch_dependents();
     const int m_tiles = (p.c_out + 127) / 128;
     const int n_tiles = (p.c_in + kBlockN - 1) / kBlockN;
     const int p_tiles = p.tiles_w * p.tiles_h * p.tiles_n;
@@ -622,6 +627,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_const
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = sm.tmem_base;
+    pdl_wait();  // everything above is independent of the previous kernel's output
 
     // tile -> (nt, mt, tap, split): the split index is slowest, so concurrently running CTAs share pixels
     auto decode = [&](int tile, int& nt, int& mt, int& tap, int& sp) {
@@ -858,19 +864,8 @@ static int launch_splitk(const CUtensorMap& map_a, const CUtensorMap& map_b, con
         if (int rc = set_smem(kernel, smem)) return rc;
         configured = true;
     }
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)(tiles * kSplit));
-    cfg.blockDim = dim3(kConvThreads);
-    cfg.dynamicSmemBytes = smem;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = kSplit;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    DLS_CHECK(cudaLaunchKernelEx(&cfg, kernel, map_a, map_b, p, (__nv_bfloat16*)out, bias, stats));
+    DLS_CHECK(launch_pdl(kernel, dim3((unsigned)(tiles * kSplit)), dim3(kConvThreads), smem, st, kSplit, map_a, map_b, p,
+                         (__nv_bfloat16*)out, bias, stats));
     return 0;
 }
 
@@ -964,8 +959,8 @@ extern "C" int dls_conv_fprop(const void* x, const void* w, void* y, const float
             if (int rc = set_smem(conv_igemm_kernel<BN, false>, smem)) return rc;                             \
             configured = true;                                                                                \
         }                                                                                                     \
-        conv_igemm_kernel<BN, false><<<grid, kConvThreads, smem, st>>>(map_a, map_b, p, (__nv_bfloat16*)y,    \
-                                                                       bias, stats);                          \
+        DLS_CHECK(launch_pdl(conv_igemm_kernel<BN, false>, grid, dim3(kConvThreads), smem, st, 0, map_a, map_b, p, \
+                             (__nv_bfloat16*)y, bias, stats));                                                \
     } while (0)
     if (block_n == 128) DLS_CONV_LAUNCH(128);
     else DLS_CONV_LAUNCH(64);
@@ -1033,8 +1028,8 @@ extern "C" int dls_conv_dgrad(const void* dy, const void* w, void* dx, const Dls
             if (int rc = set_smem(conv_igemm_kernel<BN, true>, smem)) return rc;                              \
             configured = true;                                                                                \
         }                                                                                                     \
-        conv_igemm_kernel<BN, true><<<grid, kConvThreads, smem, st>>>(map_a, map_b, p, (__nv_bfloat16*)dx,    \
-                                                                      nullptr, nullptr);                      \
+        DLS_CHECK(launch_pdl(conv_igemm_kernel<BN, true>, grid, dim3(kConvThreads), smem, st, 0, map_a, map_b, p, \
+                             (__nv_bfloat16*)dx, (const float*)nullptr, (float*)nullptr));                    \
     } while (0)
     if (block_n == 128) DLS_CONV_LAUNCH(128);
     else DLS_CONV_LAUNCH(64);
@@ -1099,7 +1094,8 @@ extern "C" int dls_conv_wgrad(const void* dy, const void* x, void* dw_out, const
             if (int rc = set_smem(conv_wgrad_kernel<BN, STAGES>, smem)) return rc;                            \
             configured = true;                                                                                \
         }                                                                                                     \
-        conv_wgrad_kernel<BN, STAGES><<<grid, kConvThreads, smem, st>>>(map_dy, map_x, p, dw);                \
+        DLS_CHECK(launch_pdl(conv_wgrad_kernel<BN, STAGES>, grid, dim3(kConvThreads), smem, st, 0, map_dy, map_x, \
+                             p, dw));                                                                         \
     } while (0)
     if (block_n == 128) DLS_WGRAD_LAUNCH(128, 3);
     else DLS_WGRAD_LAUNCH(64, 4);

@@ -23,6 +23,8 @@ sgd_step_kernel(float* __restrict__ params, float* __restrict__ mom, const float
                 const long long* __restrict__ tensor_offsets, int n_tensors, const float* __restrict__ lr_table,
                 int lr_len, const int32_t* __restrict__ state, float weight_decay, float momentum, float dampening,
                 int nesterov, const uint8_t* __restrict__ grad_is_bf16, __nv_bfloat16* __restrict__ shadow) {
+    pdl_launch_dependents();
+    pdl_wait();
     extern __shared__ long long s_off[];
     for (int i = threadIdx.x; i <= n_tensors; i += blockDim.x) s_off[i] = tensor_offsets[i];
     __syncthreads();
@@ -110,6 +112,8 @@ sgd_step_kernel(float* __restrict__ params, float* __restrict__ mom, const float
 }
 
 __global__ void sgd_tick_kernel(int32_t* state) {
+    pdl_launch_dependents();
+    pdl_wait();
     state[0] += 1;  // optimizer / LR-schedule step
     state[1] = 1;   // momentum buffer is initialised from now on
     state[2] += 1;  // batch index inside the epoch (the host zeroes it per epoch)
@@ -121,6 +125,8 @@ gather_batch_kernel(const float* __restrict__ x_all, const long long* __restrict
                     const long long* __restrict__ order, long long n_order, const int32_t* __restrict__ state,
                     int state_index, int batch_stride, long long row_elems, int channels,
                     float* __restrict__ x_out, long long* __restrict__ y_out) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int b = blockIdx.x;
     // batch_stride is the epoch's regular batch size: the (smaller) last batch starts at
     // index * stride too
@@ -151,6 +157,8 @@ gather_batch_kernel(const float* __restrict__ x_all, const long long* __restrict
 __global__ void __launch_bounds__(256)
 metric_accumulate_kernel(const float* __restrict__ logits, const long long* __restrict__ targets,
                          const float* __restrict__ loss, int batch, int classes, double* __restrict__ acc) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     int correct = 0;
@@ -198,17 +206,15 @@ extern "C" int dls_sgd_step(float* params, float* momentum_buf, const float* con
     const size_t smem = (size_t)(n_tensors + 1) * sizeof(long long);
     // grid from the arena size is unknown on the host without a sync: a fixed persistent grid
     const int grid = kNumSMs * 8;
-    sgd_step_kernel<<<grid, kSgdThreads, smem, (cudaStream_t)stream>>>(params, momentum_buf, grads, tensor_offsets,
-                                                                         n_tensors, lr_table, lr_len, state,
-                                                                         weight_decay, momentum, dampening, nesterov,
-                                                                         grad_is_bf16,
-                                                                         reinterpret_cast<__nv_bfloat16*>(shadow_bf16));
+    DLS_CHECK(launch_pdl(sgd_step_kernel, dim3(grid), dim3(kSgdThreads), smem, (cudaStream_t)stream, 0, params,
+                         momentum_buf, grads, tensor_offsets, n_tensors, lr_table, lr_len, state, weight_decay, momentum,
+                         dampening, nesterov, grad_is_bf16, reinterpret_cast<__nv_bfloat16*>(shadow_bf16)));
     DLS_LAUNCHED("sgd_step_kernel");
     return 0;
 }
 
 extern "C" int dls_sgd_tick(int32_t* state, void* stream) {
-    sgd_tick_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(state);
+    DLS_CHECK(launch_pdl(sgd_tick_kernel, dim3(1), dim3(1), 0, (cudaStream_t)stream, 0, state));
     DLS_LAUNCHED("sgd_tick_kernel");
     return 0;
 }
@@ -231,7 +237,8 @@ extern "C" int dls_metric_accumulate(const float* logits, const long long* targe
     if (batch < 1 || classes < 1) return fail_msg("dls_metric_accumulate: empty batch");
     const int warps_per_block = 8;
     const int grid = (batch + warps_per_block - 1) / warps_per_block;
-    metric_accumulate_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(logits, targets, loss, batch, classes, acc);
+    DLS_CHECK(launch_pdl(metric_accumulate_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, 0, logits, targets,
+                         loss, batch, classes, acc));
     DLS_LAUNCHED("metric_accumulate_kernel");
     return 0;
 }

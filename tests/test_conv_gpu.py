@@ -94,13 +94,13 @@ def test_direct_module(n, ci, h, w, co, k, st, pad, bias, amp):
     dev = torch.device("cuda", 0)
     torch.manual_seed(n + ci + co)
     conv = nn.Conv2d(ci, co, k, st, pad, bias=bias).to(dev)
-    ref = nn.Conv2d(ci, co, k, st, pad, bias=bias).to(dev)
+    ref = nn.Conv2d(ci, co, k, st, pad, bias=bias).to(dev).double()  # fp64 oracle (cuDNN's fp32 path is TF32)
     ref.load_state_dict(conv.state_dict())
     C.install(conv)
     x = torch.randn(n, ci, h, w, device=dev)
     if ci > 1:
         x = x.contiguous(memory_format=torch.channels_last)
-    x1, x2 = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    x1, x2 = x.clone().requires_grad_(True), x.double().requires_grad_(True)
     before = C.STATS["direct"]
     with torch.autocast("cuda", dtype=torch.bfloat16, enabled=amp):
         y = conv(x1)
@@ -110,11 +110,12 @@ def test_direct_module(n, ci, h, w, co, k, st, pad, bias, amp):
     y.backward(g.to(y.dtype))
     yr.backward(g)
     tol = 2e-2 if amp else 1e-4
-    torch.testing.assert_close(y.float(), yr, rtol=tol, atol=tol)
-    torch.testing.assert_close(x1.grad, x2.grad, rtol=tol, atol=tol * float(x2.grad.abs().max()))
-    torch.testing.assert_close(conv.weight.grad, ref.weight.grad, rtol=tol, atol=tol * float(ref.weight.grad.abs().max()))
+    torch.testing.assert_close(y.double(), yr, rtol=tol, atol=tol)
+    torch.testing.assert_close(x1.grad.double(), x2.grad, rtol=tol, atol=tol * float(x2.grad.abs().max()))
+    torch.testing.assert_close(conv.weight.grad.double(), ref.weight.grad, rtol=tol,
+                               atol=tol * float(ref.weight.grad.abs().max()))
     if bias:
-        torch.testing.assert_close(conv.bias.grad, ref.bias.grad, rtol=tol, atol=tol * float(ref.bias.grad.abs().max()))
+        torch.testing.assert_close(conv.bias.grad.double(), ref.bias.grad, rtol=tol, atol=tol * float(ref.bias.grad.abs().max()))
 
 
 def test_module_path_matches_autocast_reference():
