@@ -2,6 +2,7 @@
 "executor" concept: a model bound to a dataset collection, a phase, a device, hooks and
 a performance metric; contract reconstructed from the call sites listed in SURVEY.md 2.3).
 """
+import os
 from dataclasses import dataclass
 from typing import Any
 
@@ -160,6 +161,67 @@ class ModelExecutor(HookCollection):
             loss = self.loss_fun(output.float(), batch.targets)
         return output, loss
 
+    # ---- evaluation as CUDA-graph replays ----------------------------------------------------------
+    def _graph_eval_batch(self, batch: Batch, metric: PerformanceMetric) -> bool:
+        """Evaluates one image batch by replaying a captured forward + loss + metric-accumulation graph (one
+        graph per batch shape; the eager path costs ~25 us of host time per kernel, ~3 ms per batch).  Returns
+        False when the batch does not qualify -- the caller then takes the eager path."""
+        if self._device.type != "cuda" or not self.hook_config.use_cuda_graph or not self.hook_config.use_fused_kernels:
+            return False
+        if os.environ.get("DLS_EVAL_GRAPH", "1") == "0" or len(batch.inputs) != 1 or batch.kwargs \
+                or batch.output_rows is not None:
+            return False
+        x = batch.inputs[0]
+        if not (isinstance(x, torch.Tensor) and x.dim() == 4 and x.is_floating_point() and x.is_cuda):
+            return False
+        from ..ops import runtime
+        from ..ops import sgd as sgd_ops
+
+        if not runtime.available():
+            return False
+        graphs = self.__dict__.setdefault("_eval_graphs", {})
+        first = next(self._model.parameters(), None)
+        key = (tuple(x.shape), x.dtype, tuple(x.stride()), bool(self.hook_config.use_amp),
+               None if first is None else (first.data_ptr(), first.dtype))  # a re-homed model gets a fresh capture
+        entry = graphs.get(key)
+        if entry is None:
+            static_x = torch.empty_strided(x.shape, x.stride(), dtype=x.dtype, device=x.device)
+            static_y = torch.empty_like(batch.targets)
+            acc = torch.zeros(3, dtype=torch.float64, device=x.device)
+
+            stats_floats = sum(2 * m.out_channels for m in self._model.modules() if type(m) is nn.Conv2d)
+            stats_buf = torch.zeros(max(stats_floats, 1), dtype=torch.float32, device=x.device)
+
+            def run() -> None:
+                stats_buf.zero_()  # BatchNorm statistics of the convolution epilogues: one fill per batch
+                with self._autocast(), conv_ops.stats_arena(stats_buf):
+                    output = self._model(static_x)
+                    loss = self.loss_fun(output.float(), static_y)
+                sgd_ops.metric_accumulate(output.float().contiguous(), static_y, loss.detach().reshape(1), acc)
+
+            with capture_guard.exclusive():
+                static_x.copy_(x)
+                static_y.copy_(batch.targets)
+                side = torch.cuda.Stream(device=self._device)
+                side.wait_stream(torch.cuda.current_stream(self._device))
+                with torch.cuda.stream(side):
+                    for _ in range(2):
+                        run()
+                torch.cuda.current_stream(self._device).wait_stream(side)
+                torch.cuda.synchronize(self._device)
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph, capture_error_mode="thread_local"):
+                    run()
+                torch.cuda.synchronize(self._device)
+            entry = graphs[key] = (graph, static_x, static_y, acc)
+        graph, static_x, static_y, acc = entry
+        static_x.copy_(x, non_blocking=True)
+        static_y.copy_(batch.targets, non_blocking=True)
+        acc.zero_()
+        graph.replay()
+        metric.accumulator.add_(acc)
+        return True
+
     def _loader(self, phase: MachineLearningPhase) -> Any:
         batch_size = self._hyper_parameter.batch_size
         if phase != MachineLearningPhase.Training:
@@ -178,10 +240,12 @@ class ModelExecutor(HookCollection):
         with self._stream_context():
             self._model_util.refresh_shadow()  # the fp32 arena may have been written in place since
         with torch.no_grad(), self._stream_context():
-            with capture_guard.shared():
-                metric.start_epoch(self._device)
-                if self._dc.get_dataset_size(phase) > 0:
-                    for batch in self._loader(phase):
+            metric.start_epoch(self._device)
+            if self._dc.get_dataset_size(phase) > 0:
+                for batch in self._loader(phase):
+                    if self._graph_eval_batch(batch, metric):
+                        continue
+                    with capture_guard.shared():
                         output, loss = self._forward(batch)
                         metric.add_batch(loss, output, batch.targets)
             if reducer is not None:  # a collective with other ranks: never while holding the guard
