@@ -210,7 +210,7 @@ class ModelExecutor(HookCollection):
                 torch.cuda.current_stream(self._device).wait_stream(side)
                 torch.cuda.synchronize(self._device)
                 graph = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(graph, capture_error_mode="thread_local"):
+                with torch.cuda.graph(graph, stream=side, capture_error_mode="thread_local"):
                     run()
                 torch.cuda.synchronize(self._device)
             entry = graphs[key] = (graph, static_x, static_y, acc)

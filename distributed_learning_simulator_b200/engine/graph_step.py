@@ -209,7 +209,9 @@ class GraphTrainStep:
         torch.cuda.synchronize(self.device)
         graph = torch.cuda.CUDAGraph()
         own_before = runtime.launch_count()
-        with torch.cuda.graph(graph, capture_error_mode="thread_local"):
+        # an explicit capture stream on THIS device: torch's default capture stream is a process-wide singleton
+        # that lives on whichever device captured first
+        with torch.cuda.graph(graph, stream=side, capture_error_mode="thread_local"):
             self._one_step(step, x_all, y_all, n_order)
         step.own_kernels = runtime.launch_count() - own_before  # own kernel nodes in one replay
         self._fill_grad_table(step)

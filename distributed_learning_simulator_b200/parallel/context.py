@@ -138,6 +138,10 @@ class ArenaPayload(dict):
 
 class DistributedContext:
     def __init__(self) -> None:
+        self._verdict_host: torch.Tensor | None = None
+        self._verdict_event: Any = None
+        self._verdict_pending = False
+        self.two_stage_reductions = 0
         self._agg_checks_left = int(os.environ.get("DLS_AGG_CHECK", "0"))
         self.agg_max_abs_err = 0.0
         self.agg_checks_done = 0
@@ -192,7 +196,8 @@ class DistributedContext:
         self.layout = layout
         self.slots = -(-worker_number // self.world)
         self.row_bytes = ((layout.total * 4 + 255) // 256) * 256
-        self.arena = SymmetricBuffer(self, self.row_bytes * self.slots)
+        # slots upload rows + one row for this rank's pre-reduced partial (two-stage reduction)
+        self.arena = SymmetricBuffer(self, self.row_bytes * (self.slots + 1))
         self.globals = self._global_buffers(self.row_bytes * 2)
         self.flags = SymmetricBuffer(self, 256)
         self._flag_table = runtime.pointer_table(self.flags.ptrs, self.device)
@@ -241,6 +246,24 @@ class DistributedContext:
                    old_scale: float, inv_total: float) -> FlatParameter:
         assert self.globals is not None and self.layout is not None and self.flags is not None
         n = self.layout.total
+        self._check_previous_verdict()
+        all_payloads, all_weights = payloads, weights
+        if len(payloads) > self.world and os.environ.get("DLS_TWO_STAGE", "1") != "0":
+            # Two-stage: many workers per GPU.  Stage 1 folds this rank's own rows into ONE weighted fp32 partial
+            # (local HBM traffic only); stage 2 is the cross-GPU kernel over the G partials, so NVLink carries
+            # (G - 1) / G of a row per GPU instead of a share of every remote worker's row.
+            from ..ops.reduce import reduce_rows_f32
+
+            mine = [(p.local, w) for p, w in zip(payloads, weights) if p.rank == self.rank and p.local is not None]
+            partial = self.arena_row(self.slots)
+            if mine:
+                reduce_rows_f32([r for r, _ in mine], [w for _, w in mine], None, 0.0, 1.0, out=partial, check_nan=False)
+            else:
+                partial.zero_()
+            self.two_stage_reductions += 1
+            payloads = [ArenaPayload(r, self.slots, self.arena.ptr(r, self.slots * self.row_bytes), self.layout,
+                                     partial if r == self.rank else None) for r in range(self.world)]
+            weights = [1.0] * self.world
         self.global_index ^= 1
         off = self.global_index * self.row_bytes
         if old is not None and old.data_ptr() == self.globals.local_ptr + off:
@@ -277,7 +300,7 @@ class DistributedContext:
             # all-reduce of every rank's locally weighted rows
             self._agg_checks_left -= 1
             acc = torch.zeros(n, dtype=torch.float64, device=self.device)
-            for payload, wt in zip(payloads, weights):
+            for payload, wt in zip(all_payloads, all_weights):
                 if payload.rank == self.rank and payload.local is not None:
                     acc.add_(payload.local.double(), alpha=float(wt))
             dist.all_reduce(acc)
@@ -287,11 +310,31 @@ class DistributedContext:
             got = self.globals.local_tensor(torch.float32, n, off).double()
             self.agg_max_abs_err = max(self.agg_max_abs_err, float((got - acc).abs().max().item()))
             self.agg_checks_done += 1
-        verdict = self.flags.local_tensor(torch.int32, 32)[16:25].cpu().tolist()
+        # the kernel's verdict words (NaN per rank, barrier time-out) are read back without stalling the round:
+        # an asynchronous copy now, the check when the next reduction starts (or at finish_reductions())
+        if self._verdict_host is None:
+            self._verdict_host = torch.zeros(9, dtype=torch.int32).pin_memory()
+            self._verdict_event = torch.cuda.Event()
+        self._verdict_host.copy_(self.flags.local_tensor(torch.int32, 32)[16:25], non_blocking=True)
+        self._verdict_event.record(torch.cuda.current_stream(self.device))
+        self._verdict_pending = True
+        if os.environ.get("DLS_SYNC_VERDICT", "0") == "1":
+            self._check_previous_verdict()
+        return FlatParameter(self.globals.local_tensor(torch.float32, n, off), self.layout)
+
+    def _check_previous_verdict(self) -> None:
+        if not self._verdict_pending:
+            return
+        self._verdict_pending = False
+        self._verdict_event.synchronize()
+        verdict = self._verdict_host.tolist()
         if verdict[8]:
             raise RuntimeError("peer barrier timed out inside fedavg_reduce (a rank is missing)")
         assert not any(verdict[: self.world]), "NaN in aggregated parameters"
-        return FlatParameter(self.globals.local_tensor(torch.float32, n, off), self.layout)
+
+    def finish_reductions(self) -> None:
+        """Check the verdict of the last fused reduction (called when a run ends)."""
+        self._check_previous_verdict()
 
     # ---- small collectives -------------------------------------------------------------------
     def all_reduce_sum(self, t: torch.Tensor) -> torch.Tensor:

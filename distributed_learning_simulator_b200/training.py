@@ -127,6 +127,10 @@ def train(config: Any, practitioners: None | set = None) -> int | None:
         return task_id
     task.wait()
     task.raise_errors()
+    from .parallel import context as dist_context
+
+    if dist_context.current() is not None:
+        dist_context.current().finish_reductions()  # verdict of the last fused cross-GPU reduction
     _write_trace(config)
     _last_results.clear()
     _last_results.update(task.results)

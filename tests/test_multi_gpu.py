@@ -61,14 +61,15 @@ if ctx.multicast:
     ctx.fence()
 with open(os.path.join({out!r}, "p2p_%d.json" % ctx.rank), "w") as f:
     json.dump({{"errs": errs, "reductions": ctx.p2p_reductions, "multicast": ctx.multicast,
-               "multicast_reductions": ctx.multicast_reductions, "bcast_err": bcast_err}}, f)
+               "multicast_reductions": ctx.multicast_reductions, "bcast_err": bcast_err,
+               "two_stage": ctx.two_stage_reductions}}, f)
 
 from distributed_learning_simulator_b200 import load_config_from_dict, train
 from distributed_learning_simulator_b200.training import get_last_training_result
 conf = {{"dataset_name": "MNIST", "model_name": "LeNet5", "distributed_algorithm": "fed_avg",
-        "optimizer_name": "SGD", "learning_rate_scheduler_name": "CosineAnnealingLR", "worker_number": 4,
+        "optimizer_name": "SGD", "learning_rate_scheduler_name": "CosineAnnealingLR", "worker_number": 2 * ctx.world,
         "batch_size": 32, "round": 3, "epoch": 1, "learning_rate": 0.1, "log_level": "WARNING",
-        "dataset_kwargs": {{"train_size": 1280, "test_size": 400}}}}
+        "dataset_kwargs": {{"train_size": 640 * ctx.world, "test_size": 400}}}}
 before = ctx.p2p_reductions
 train(load_config_from_dict(conf))
 res = get_last_training_result()
@@ -85,14 +86,16 @@ def _free_port() -> int:
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
-@pytest.mark.parametrize("nvls", ["1", "0"])
-def test_p2p_reduce_and_distributed_training(tmp_path, nvls):
+@pytest.mark.parametrize("nvls,two_stage,world", [("1", "1", 2), ("0", "1", 2), ("0", "0", 2), ("0", "1", 4), ("1", "1", 8)])
+def test_p2p_reduce_and_distributed_training(tmp_path, nvls, two_stage, world):
     """nvls=1: the broadcast half of the fused kernel is one multimem.st per vector (NVSwitch multicast)
-    when the platform offers it; nvls=0: one peer store per destination.  Same results either way."""
-    world = 2
+    when the platform offers it; nvls=0: one peer store per destination.  two_stage=1: each rank folds its own
+    2-3 rows into one partial before the cross-GPU kernel; 0: every row crosses NVLink.  Same results either way."""
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
     script = tmp_path / "run.py"
     script.write_text(SCRIPT.format(root=ROOT, out=str(tmp_path)))
-    env = dict(os.environ, DLS_OUTPUT_ROOT=str(tmp_path), DLS_NVLS=nvls, DLS_NVLS_REDUCE=nvls)
+    env = dict(os.environ, DLS_OUTPUT_ROOT=str(tmp_path), DLS_NVLS=nvls, DLS_NVLS_REDUCE=nvls, DLS_TWO_STAGE=two_stage)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), str(script)]
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
@@ -100,13 +103,12 @@ def test_p2p_reduce_and_distributed_training(tmp_path, nvls):
     for r in range(world):
         p2p = json.load(open(tmp_path / f"p2p_{r}.json"))
         assert max(p2p["errs"]) < 1e-5, p2p
-        assert p2p["reductions"] == 3
+        assert p2p["reductions"] == 3 and p2p["two_stage"] == (3 if two_stage == "1" else 0)
         if nvls == "0":
             assert not p2p["multicast"] and p2p["multicast_reductions"] == 0
         elif p2p["multicast"]:
             assert p2p["multicast_reductions"] == 3 and p2p["bcast_err"] == 0.0
         print("multicast available:", p2p["multicast"])
-    t0, t1 = (json.load(open(tmp_path / f"train_{r}.json")) for r in range(world))
-    assert t0["performance"] == t1["performance"]
-    assert t0["p2p_reductions"] == 3 and t1["p2p_reductions"] == 3
-    assert t0["performance"]["3"]["test_accuracy"] > 0.2
+    runs = [json.load(open(tmp_path / f"train_{r}.json")) for r in range(world)]
+    assert all(t["performance"] == runs[0]["performance"] and t["p2p_reductions"] == 3 for t in runs)
+    assert runs[0]["performance"]["3"]["test_accuracy"] > 0.2
