@@ -197,7 +197,6 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     Smem& sm = *reinterpret_cast<Smem*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    pdl_launch_dependents();
     const int cblocks = (p.a_channels + kGemmBlockK - 1) / kGemmBlockK;
     const int n_tiles = (p.n_out + kBlockN - 1) / kBlockN;
     const int p_tiles = p.tiles_w * p.tiles_h * p.tiles_n;
@@ -226,6 +225,9 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = sm.tmem_base;
+    // Let the next kernel of the stream launch only now that this CTA owns its tensor memory: a dependent that
+    // were resident earlier could take the columns this CTA is still waiting for and then wait for this grid.
+    pdl_launch_dependents();
     pdl_wait();  // everything above is independent of the previous kernel's output
 
     if (warp == 0) {
@@ -390,7 +392,6 @@ conv_igemm_splitk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
     Smem& sm = *reinterpret_cast<Smem*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    pdl_launch_dependents();
     const int crank = (int)cluster_rank();
     const int cblocks = (p.a_channels + kGemmBlockK - 1) / kGemmBlockK;
     const int n_tiles = (p.n_out + kBlockN - 1) / kBlockN;
@@ -426,6 +427,9 @@ conv_igemm_splitk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = sm.tmem_base;
+    // Let the next kernel of the stream launch only now that this CTA owns its tensor memory: a dependent that
+    // were resident earlier could take the columns this CTA is still waiting for and then wait for this grid.
+    pdl_launch_dependents();
     pdl_wait();  // everything above is independent of the previous kernel's output
     const int w0 = (pt % p.tiles_w) * p.bw;
     const int h0 = ((pt / p.tiles_w) % p.tiles_h) * p.bh;
@@ -519,7 +523,10 @@ conv_igemm_splitk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
                     : "=r"(done)
                     : "r"(recv_bar), "r"(0u)
                     : "memory");
-                if (spins > 20000000u) asm volatile("trap;");
+                if (spins > 200000000u) {
+                    printf("dls: split-K receive barrier timed out (block %d thread %d)\n", (int)blockIdx.x, (int)threadIdx.x);
+                    asm volatile("trap;");
+                }
             }
         }
         const int lw = m_local % p.bw, lh = (m_local / p.bw) % p.bh, ln = m_local / (p.bw * p.bh);
@@ -598,7 +605,6 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_const
     Smem& sm = *reinterpret_cast<Smem*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    pdl_launch_dependents();
     const int m_tiles = (p.c_out + 127) / 128;
     const int n_tiles = (p.c_in + kBlockN - 1) / kBlockN;
     const int p_tiles = p.tiles_w * p.tiles_h * p.tiles_n;
@@ -627,6 +633,9 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_const
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = sm.tmem_base;
+    // Let the next kernel of the stream launch only now that this CTA owns its tensor memory: a dependent that
+    // were resident earlier could take the columns this CTA is still waiting for and then wait for this grid.
+    pdl_launch_dependents();
     pdl_wait();  // everything above is independent of the previous kernel's output
 
     // tile -> (nt, mt, tap, split): the split index is slowest, so concurrently running CTAs share pixels

@@ -37,7 +37,11 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
             : "r"(addr), "r"(parity)
             : "memory");
         if (done) return;
-        if (spins > 20000000u) asm volatile("trap;");
+        if (spins > 200000000u) {  // tens of seconds: a protocol bug, not a busy GPU
+            printf("dls: mbarrier wait timed out (block %d thread %d barrier 0x%x parity %u)\n", (int)blockIdx.x,
+                   (int)threadIdx.x, addr, parity);
+            asm volatile("trap;");
+        }
     }
 }
 

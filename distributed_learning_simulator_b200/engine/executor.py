@@ -210,11 +210,13 @@ class ModelExecutor(HookCollection):
                 torch.cuda.current_stream(self._device).wait_stream(side)
                 torch.cuda.synchronize(self._device)
                 graph = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(graph, stream=side, capture_error_mode="thread_local"):
+                with torch.cuda.graph(graph, stream=torch.cuda.Stream(device=self._device),
+                                      capture_error_mode="thread_local"):
                     run()
                 torch.cuda.synchronize(self._device)
-            entry = graphs[key] = (graph, static_x, static_y, acc)
-        graph, static_x, static_y, acc = entry
+            # everything the captured kernels address must live as long as the graph (stats_buf included)
+            entry = graphs[key] = (graph, static_x, static_y, acc, stats_buf)
+        graph, static_x, static_y, acc, _ = entry
         static_x.copy_(x, non_blocking=True)
         static_y.copy_(batch.targets, non_blocking=True)
         acc.zero_()

@@ -211,7 +211,7 @@ class GraphTrainStep:
         own_before = runtime.launch_count()
         # an explicit capture stream on THIS device: torch's default capture stream is a process-wide singleton
         # that lives on whichever device captured first
-        with torch.cuda.graph(graph, stream=side, capture_error_mode="thread_local"):
+        with torch.cuda.graph(graph, stream=torch.cuda.Stream(device=self.device), capture_error_mode="thread_local"):
             self._one_step(step, x_all, y_all, n_order)
         step.own_kernels = runtime.launch_count() - own_before  # own kernel nodes in one replay
         self._fill_grad_table(step)
