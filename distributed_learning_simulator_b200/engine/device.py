@@ -145,3 +145,21 @@ class CaptureGuard:
 
 
 capture_guard = CaptureGuard()
+
+
+_capture_streams: dict = {}
+_capture_streams_lock = threading.Lock()
+
+
+def capture_stream(device: "torch.device") -> "torch.cuda.Stream":
+    """ONE capture stream per device for the whole process, never destroyed.  torch's own default capture
+    stream is a singleton on whichever device captured first (wrong device for the others), and a fresh stream
+    per capture is worse: cuBLAS / cuDNN workspaces are cached per (handle, stream) and a workspace handed out
+    during one capture comes from THAT graph's private pool -- a later stream that reuses the address would make
+    another graph point into it.  Captures are serialised by ``capture_guard.exclusive()``."""
+    index = device.index if device.index is not None else torch.cuda.current_device()
+    with _capture_streams_lock:
+        stream = _capture_streams.get(index)
+        if stream is None:
+            stream = _capture_streams[index] = torch.cuda.Stream(device=torch.device("cuda", index))
+    return stream

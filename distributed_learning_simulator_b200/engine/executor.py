@@ -11,7 +11,7 @@ from torch import nn
 
 from .dataloader import Batch, create_loader
 from .dataset import DatasetCollection
-from .device import capture_guard
+from .device import capture_guard, capture_stream
 from .hook import HookCollection
 from .hyper_parameter import HyperParameter
 from .metric import PerformanceMetric
@@ -210,8 +210,7 @@ class ModelExecutor(HookCollection):
                 torch.cuda.current_stream(self._device).wait_stream(side)
                 torch.cuda.synchronize(self._device)
                 graph = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(graph, stream=torch.cuda.Stream(device=self._device),
-                                      capture_error_mode="thread_local"):
+                with torch.cuda.graph(graph, stream=capture_stream(self._device), capture_error_mode="thread_local"):
                     run()
                 torch.cuda.synchronize(self._device)
             # everything the captured kernels address must live as long as the graph (stats_buf included)

@@ -23,7 +23,7 @@ from ..ops import conv as conv_ops
 from ..ops import runtime
 from ..ops import sgd as sgd_ops
 from .dataloader import SampleLoader
-from .device import capture_guard
+from .device import capture_guard, capture_stream
 from .ml_type import ExecutorHookPoint, MachineLearningPhase
 
 
@@ -209,9 +209,8 @@ class GraphTrainStep:
         torch.cuda.synchronize(self.device)
         graph = torch.cuda.CUDAGraph()
         own_before = runtime.launch_count()
-        # an explicit capture stream on THIS device: torch's default capture stream is a process-wide singleton
-        # that lives on whichever device captured first
-        with torch.cuda.graph(graph, stream=torch.cuda.Stream(device=self.device), capture_error_mode="thread_local"):
+        # the per-device capture stream (engine/device.py)
+        with torch.cuda.graph(graph, stream=capture_stream(self.device), capture_error_mode="thread_local"):
             self._one_step(step, x_all, y_all, n_order)
         step.own_kernels = runtime.launch_count() - own_before  # own kernel nodes in one replay
         self._fill_grad_table(step)
