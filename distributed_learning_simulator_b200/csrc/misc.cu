@@ -1,4 +1,6 @@
 // sign_SGD packing / majority vote, FedDropoutAvg masking, FedOBD block scores.
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 #include "../../include/dls_b200.h"
 
@@ -28,6 +30,43 @@ sign_majority_kernel(const uint32_t* const* __restrict__ rows, int n_rows, long 
         for (int k = 0; k < n_rows; ++k) neg += (rows[k][w] >> lane) & 1u;  // one broadcast load per warp
         const int s = n_rows - 2 * neg;
         if (i < n) vote[i] = s > 0 ? 1.f : (s < 0 ? -1.f : 0.f);
+    }
+}
+
+// signSGD step in one pass: majority vote over the K workers' packed sign words (rows may live in peer GPUs'
+// memory: plain loads over NVLink) fused with the optimizer update of THIS worker's parameters -- momentum,
+// dampening, nesterov, p -= lr * d, and the bf16 compute shadow when there is one.  Replaces the server-side
+// vote launch, the fp32 vote tensor (4 bytes per parameter written once and read by every worker) and the
+// separate update launch of the scaffold (reference: worker/gradient_worker.py:96-116 applies the update with
+// a Python loop over parameter tensors).
+__global__ void __launch_bounds__(256)
+sign_vote_sgd_kernel(const uint32_t* const* __restrict__ rows, int n_rows, long long n, float* __restrict__ params,
+                     float* __restrict__ mom, float lr, float momentum, float dampening, int nesterov, int mom_ready,
+                     __nv_bfloat16* __restrict__ shadow, const uint8_t* __restrict__ shadow_mask,
+                     const long long* __restrict__ tensor_offsets, int n_tensors) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const int lane = threadIdx.x & 31;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i - lane < n;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long w = i >> 5;
+        int neg = 0;
+        for (int k = 0; k < n_rows; ++k) neg += (rows[k][w] >> lane) & 1u;  // one broadcast load per warp
+        if (i >= n) continue;
+        const int s = n_rows - 2 * neg;
+        float d = s > 0 ? 1.f : (s < 0 ? -1.f : 0.f);
+        if (momentum != 0.f) {
+            const float m = mom_ready ? momentum * mom[i] + (1.f - dampening) * d : d;
+            mom[i] = m;
+            d = nesterov ? d + momentum * m : m;
+        }
+        const float p = params[i] - lr * d;
+        params[i] = p;
+        if (shadow != nullptr) {
+            bool shadowed = true;
+            if (shadow_mask != nullptr) shadowed = shadow_mask[find_segment(tensor_offsets, n_tensors, i)] != 0;
+            if (shadowed) shadow[i] = __float2bfloat16(p);
+        }
     }
 }
 
@@ -118,6 +157,21 @@ extern "C" int dls_sign_majority(const uint32_t* const* rows, int n_rows, long l
     if (n < 1 || n_rows < 1) return fail_msg("dls_sign_majority: empty input");
     sign_majority_kernel<<<grid_for(n, 256, 8), 256, 0, (cudaStream_t)stream>>>(rows, n_rows, n, vote);
     DLS_LAUNCHED("sign_majority_kernel");
+    return 0;
+}
+
+extern "C" int dls_sign_vote_sgd(const uint32_t* const* rows, int n_rows, long long n, float* params, float* mom,
+                                 float lr, float momentum, float dampening, int nesterov, int mom_ready, void* shadow,
+                                 const uint8_t* shadow_mask, const long long* tensor_offsets, int n_tensors,
+                                 void* stream) {
+    if (n < 1 || n_rows < 1) return fail_msg("dls_sign_vote_sgd: empty input");
+    if (momentum != 0.f && mom == nullptr) return fail_msg("dls_sign_vote_sgd: momentum buffer missing");
+    if (shadow != nullptr && shadow_mask != nullptr && (tensor_offsets == nullptr || n_tensors < 1))
+        return fail_msg("dls_sign_vote_sgd: a shadow mask needs the tensor offsets");
+    DLS_CHECK(launch_pdl(sign_vote_sgd_kernel, dim3(grid_for(n, 256, 8)), dim3(256), 0, (cudaStream_t)stream, 0, rows,
+                         n_rows, n, params, mom, lr, momentum, dampening, nesterov, mom_ready,
+                         reinterpret_cast<__nv_bfloat16*>(shadow), shadow_mask, tensor_offsets, n_tensors));
+    DLS_LAUNCHED("sign_vote_sgd_kernel");
     return 0;
 }
 

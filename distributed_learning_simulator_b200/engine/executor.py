@@ -179,6 +179,8 @@ class ModelExecutor(HookCollection):
 
         if not runtime.available():
             return False
+        if self.__dict__.get("_eval_graph_broken", False):
+            return False
         graphs = self.__dict__.setdefault("_eval_graphs", {})
         first = next(self._model.parameters(), None)
         key = (tuple(x.shape), x.dtype, tuple(x.stride()), bool(self.hook_config.use_amp),
@@ -199,20 +201,31 @@ class ModelExecutor(HookCollection):
                     loss = self.loss_fun(output.float(), static_y)
                 sgd_ops.metric_accumulate(output.float().contiguous(), static_y, loss.detach().reshape(1), acc)
 
-            with capture_guard.exclusive():
-                static_x.copy_(x)
-                static_y.copy_(batch.targets)
-                side = torch.cuda.Stream(device=self._device)
-                side.wait_stream(torch.cuda.current_stream(self._device))
-                with torch.cuda.stream(side):
-                    for _ in range(2):
+            try:
+                with capture_guard.exclusive():
+                    static_x.copy_(x)
+                    static_y.copy_(batch.targets)
+                    side = torch.cuda.Stream(device=self._device)
+                    side.wait_stream(torch.cuda.current_stream(self._device))
+                    with torch.cuda.stream(side):
+                        for _ in range(2):
+                            run()
+                    torch.cuda.current_stream(self._device).wait_stream(side)
+                    torch.cuda.synchronize(self._device)
+                    graph = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(graph, stream=capture_stream(self._device), capture_error_mode="thread_local"):
                         run()
-                torch.cuda.current_stream(self._device).wait_stream(side)
+                    torch.cuda.synchronize(self._device)
+            except RuntimeError as e:
+                # a capture that another role's eager library call invalidated: this executor evaluates eagerly
+                # from now on (correct, just ~3 ms of host time per batch slower)
+                from .log import get_logger
+
+                get_logger().warning("evaluation graph capture failed, falling back to eager evaluation: %s",
+                                     str(e).splitlines()[0])
+                self.__dict__["_eval_graph_broken"] = True
                 torch.cuda.synchronize(self._device)
-                graph = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(graph, stream=capture_stream(self._device), capture_error_mode="thread_local"):
-                    run()
-                torch.cuda.synchronize(self._device)
+                return False
             # everything the captured kernels address must live as long as the graph (stats_buf included)
             entry = graphs[key] = (graph, static_x, static_y, acc, stats_buf)
         graph, static_x, static_y, acc, _ = entry

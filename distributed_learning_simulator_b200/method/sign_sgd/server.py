@@ -23,6 +23,7 @@ class SignSGDServer(Server):
         self.__finished: set[int] = set()
         self.__stat: dict = {}
         self.vote_count = 0
+        self.fused_vote = bool(self.config.algorithm_kwargs.get("fused_vote", True))
 
     @property
     def performance_stat(self) -> dict:
@@ -47,9 +48,14 @@ class SignSGDServer(Server):
             gradients, self.__gradients = self.__gradients, {}
             n = int(next(iter(gradients.values())).other_data["numel"])
             rows = [gradients[w].other_data["gradient"] for w in sorted(gradients)]
-            vote = misc_ops.sign_majority(rows, n)
             self.vote_count += 1
-            self._endpoint.broadcast(Message(in_round=True, other_data={"gradient": vote}), worker_ids=set(gradients))
+            if self.fused_vote:
+                # no vote tensor: every worker runs the majority over the packed rows inside its own update
+                # kernel (rows of other ranks are peer-mapped words, see parallel/topology.py)
+                answer: Any = {"sign_rows": rows, "numel": n}
+            else:
+                answer = misc_ops.sign_majority([misc_ops.as_local_words(r) for r in rows], n)
+            self._endpoint.broadcast(Message(in_round=True, other_data={"gradient": answer}), worker_ids=set(gradients))
         if active and all(w in self.__epoch_reports for w in active):
             reports, self.__epoch_reports = self.__epoch_reports, {}
             epoch = next(iter(reports.values())).other_data["epoch"]

@@ -30,6 +30,22 @@ class SignSGDWorker(GradientWorker):
     def _process_gradient(self, gradient: torch.Tensor) -> Any:
         return misc_ops.sign_pack(gradient)
 
+    def _decode_gradient(self, payload: Any, numel: int) -> torch.Tensor:
+        if isinstance(payload, dict) and "sign_rows" in payload:  # no fused path here (CPU / non-flat model)
+            return misc_ops.sign_majority([misc_ops.as_local_words(r) for r in payload["sign_rows"]], numel)
+        return payload
+
+    def _apply_fused(self, result: Message, flat: torch.Tensor, momentum_buf: torch.Tensor, lr: float, hp: Any,
+                     momentum_ready: bool) -> bool:
+        """Vote + update in one launch over every worker's packed words (peer-mapped for other ranks)."""
+        payload = result.other_data.get("gradient")
+        if not (isinstance(payload, dict) and "sign_rows" in payload):
+            return False
+        util = self.trainer.model_util
+        misc_ops.sign_vote_sgd(payload["sign_rows"], flat.numel(), flat, momentum_buf if hp.momentum else None, lr,
+                               hp.momentum, 0.0, False, momentum_ready, shadow=util.shadow)
+        return True
+
     def _report_epoch(self, **kwargs: Any) -> None:
         epoch = kwargs["epoch"]
         if self.worker_id == 0:

@@ -1,5 +1,7 @@
 """Front-ends of csrc/misc.cu: sign packing / majority vote (sign_SGD), Bernoulli upload
 masking (FedDropoutAvg), per-block squared parameter change (FedOBD)."""
+from typing import Any
+
 import torch
 
 from . import runtime
@@ -42,6 +44,50 @@ def sign_majority(rows: list[torch.Tensor], n: int) -> torch.Tensor:
         runtime.call("dls_sign_majority", table.data_ptr(), len(rows), n, vote.data_ptr(), runtime.stream_ptr(device))
         return vote
     return oracle_sign_majority(rows, n)
+
+
+class PeerWords:
+    """Packed sign words that live in another rank's peer-mapped memory: usable by this framework's kernels
+    through ``data_ptr()``; ``to_local()`` copies them here for code that needs a tensor."""
+
+    def __init__(self, ptr: int, n_words: int, device: torch.device) -> None:
+        self.ptr, self.n_words, self.device = int(ptr), int(n_words), device
+
+    def data_ptr(self) -> int:
+        return self.ptr
+
+    def to_local(self) -> torch.Tensor:
+        out = torch.empty(self.n_words, dtype=torch.int32, device=self.device)
+        runtime.call("dls_copy_device", out.data_ptr(), self.ptr, self.n_words * 4, runtime.stream_ptr(self.device))
+        return out
+
+
+def as_local_words(row: Any) -> torch.Tensor:
+    return row.to_local() if isinstance(row, PeerWords) else row
+
+
+def sign_vote_sgd(rows: list, n: int, params: torch.Tensor, mom: torch.Tensor | None, lr: float, momentum: float,
+                  dampening: float = 0.0, nesterov: bool = False, mom_ready: bool = True,
+                  shadow: torch.Tensor | None = None) -> None:
+    """One launch: majority vote over the packed rows (tensors or raw device pointers, e.g. peer-mapped words of
+    other ranks) and the SGD update of ``params`` (flat fp32) with it.  CPU / no library: the torch oracle."""
+    if params.is_cuda and runtime.available():
+        table = runtime.pointer_table(rows, params.device)
+        runtime.call("dls_sign_vote_sgd", table.data_ptr(), len(rows), int(n), params.data_ptr(), runtime.ptr(mom),
+                     float(lr), float(momentum), float(dampening), int(nesterov), int(mom_ready), runtime.ptr(shadow),
+                     None, None, 0, runtime.stream_ptr(params.device))
+        return
+    d = oracle_sign_majority([r for r in rows], n)
+    if momentum != 0:
+        assert mom is not None
+        if mom_ready:
+            mom.mul_(momentum).add_(d, alpha=1 - dampening)
+        else:
+            mom.copy_(d)
+        d = d + momentum * mom if nesterov else mom
+    params.add_(d, alpha=-lr)
+    if shadow is not None:
+        shadow.copy_(params)
 
 
 def oracle_sign_majority(rows: list[torch.Tensor], n: int) -> torch.Tensor:

@@ -72,6 +72,8 @@ _SIGNATURES = {
                    c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
     "dls_sign_pack": [c_void_p, c_ll, c_void_p, c_void_p],
     "dls_sign_majority": [c_void_p, c_int, c_ll, c_void_p, c_void_p],
+    "dls_sign_vote_sgd": [c_void_p, c_int, c_ll, c_void_p, c_void_p, c_float, c_float, c_float, c_int, c_int, c_void_p,
+                          c_void_p, c_void_p, c_int, c_void_p],
     "dls_dropout_mask": [c_void_p, c_ll, c_float, c_u64, c_void_p, c_void_p, c_void_p],
     "dls_block_sqdiff": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p],
     "dls_subset_gemm_bf16": [c_void_p, c_int, c_void_p, c_int, c_ll, c_ll, c_void_p, c_int, c_int, c_int, c_void_p,

@@ -164,6 +164,9 @@ class DistributedContext:
         self.arena: SymmetricBuffer | None = None
         self.globals: SymmetricBuffer | None = None
         self.flags: SymmetricBuffer | None = None
+        self.signs: SymmetricBuffer | None = None
+        self.sign_words = 0
+        self.sign_stores_pending = False
         self.slots = 0
         self.epoch = 0
         self.global_index = 0
@@ -200,6 +203,12 @@ class DistributedContext:
         self.arena = SymmetricBuffer(self, self.row_bytes * (self.slots + 1))
         self.globals = self._global_buffers(self.row_bytes * 2)
         self.flags = SymmetricBuffer(self, 256)
+        # signSGD: two generations (step parity) of packed sign words per local worker, read by the peers' fused
+        # vote + update kernels; a worker is at most one step ahead of the slowest reader
+        self.sign_words = (layout.total + 31) // 32
+        self.sign_row_bytes = ((self.sign_words * 4 + 255) // 256) * 256
+        self.signs = SymmetricBuffer(self, 2 * self.slots * self.sign_row_bytes)
+        self.sign_stores_pending = False
         self._flag_table = runtime.pointer_table(self.flags.ptrs, self.device)
         self._nan = torch.zeros(1, dtype=torch.int32, device=self.device)
         self.epoch = 0
@@ -235,6 +244,27 @@ class DistributedContext:
         row = self.arena_row(slot)
         row.copy_(flat, non_blocking=True)
         return ArenaPayload(self.rank, slot, self.arena.ptr(self.rank, slot * self.row_bytes), self.layout, row)
+
+    def _sign_offset(self, slot: int, parity: int) -> int:
+        return ((parity & 1) * self.slots + slot) * self.sign_row_bytes
+
+    def store_sign_words(self, worker_id: int, parity: int, words: torch.Tensor) -> tuple[int, int, int]:
+        """Copy a local worker's packed sign words into the peer-mapped buffer (current stream); the caller
+        synchronises before announcing them (``flush_sign_stores``)."""
+        assert self.signs is not None and words.numel() == self.sign_words
+        slot = self.slot_of(worker_id)
+        self.signs.local_tensor(torch.int32, self.sign_words, self._sign_offset(slot, parity)).copy_(words, non_blocking=True)
+        self.sign_stores_pending = True
+        return self.rank, slot, parity & 1
+
+    def flush_sign_stores(self) -> None:
+        if self.sign_stores_pending:
+            torch.cuda.current_stream(self.device).synchronize()
+            self.sign_stores_pending = False
+
+    def sign_words_ptr(self, rank: int, slot: int, parity: int) -> int:
+        assert self.signs is not None
+        return self.signs.ptr(rank, self._sign_offset(slot, parity))
 
     def remote_payload(self, rank: int, slot: int) -> ArenaPayload:
         assert self.arena is not None and self.layout is not None

@@ -28,6 +28,13 @@ class _ArenaRef:
         self.rank, self.slot = rank, slot
 
 
+class _SignRef:
+    """Packed sign words of a signSGD step parked in the owner's peer-mapped buffer."""
+
+    def __init__(self, rank: int, slot: int, parity: int) -> None:
+        self.rank, self.slot, self.parity = rank, slot, parity
+
+
 def _to_cpu(data: Any) -> Any:
     return recursive_tensor_op(data, lambda t: t.detach().cpu())
 
@@ -56,6 +63,14 @@ class DistributedTopology(ThreadCentralTopology):
         field = "delta_parameter" if isinstance(msg, DeltaParameterMessage) else (
             "parameter" if isinstance(msg, ParameterMessage) else None)
         ctx = self.ctx
+        words = msg.other_data.get("gradient") if isinstance(getattr(msg, "other_data", None), dict) else None
+        if field is None and ctx.signs is not None and isinstance(words, torch.Tensor) and words.is_cuda \
+                and words.dtype == torch.int32 and words.numel() == ctx.sign_words and "parity" in msg.other_data:
+            # signSGD step: the words stay on the device; peers read them over NVLink inside their update kernel
+            ref = _SignRef(*ctx.store_sign_words(worker_id, int(msg.other_data["parity"]), words))
+            wire = copy.copy(msg)
+            wire.other_data = {k: (ref if k == "gradient" else _to_cpu(v)) for k, v in msg.other_data.items()}
+            return wire, msg
         if field is not None and ctx.arena is not None:
             payload = getattr(msg, field)
             flat = None
@@ -83,6 +98,12 @@ class DistributedTopology(ThreadCentralTopology):
     def _decode(self, wire: Any) -> Any:
         if wire is None or not dataclasses.is_dataclass(wire):
             return wire
+        ref = wire.other_data.get("gradient") if isinstance(getattr(wire, "other_data", None), dict) else None
+        if isinstance(ref, _SignRef):
+            from ..ops.misc import PeerWords
+
+            wire.other_data["gradient"] = PeerWords(self.ctx.sign_words_ptr(ref.rank, ref.slot, ref.parity),
+                                                    self.ctx.sign_words, self.ctx.device)
         for name in ("delta_parameter", "parameter"):
             ref = getattr(wire, name, None)
             if isinstance(ref, _ArenaRef):
@@ -122,6 +143,7 @@ class DistributedTopology(ThreadCentralTopology):
         wire: dict[int, Any] = {}
         for w, msg in local_msgs.items():
             wire[w], local_msgs[w] = self._encode(w, msg)
+        self.ctx.flush_sign_stores()
         gathered = self.ctx.exchange(wire)
         self.exchanges += 1
         for rank, part in enumerate(gathered):
@@ -141,6 +163,7 @@ class DistributedTopology(ThreadCentralTopology):
             wire: dict[int, Any] = {}
             for w, msg in local_msgs.items():
                 wire[w], local_msgs[w] = self._encode(w, msg)
+            self.ctx.flush_sign_stores()  # the words must be in memory before a peer learns about them
             gathered = self.ctx.exchange(wire)
             self.exchanges += 1
             for rank, part in enumerate(gathered):

@@ -67,6 +67,12 @@ class GradientWorker(Client):
     def _decode_gradient(self, payload: Any, numel: int) -> torch.Tensor:
         return payload
 
+    def _apply_fused(self, result: Message, flat: torch.Tensor, momentum_buf: torch.Tensor, lr: float, hp: Any,
+                     momentum_ready: bool) -> bool:
+        """Override point: decode the server's answer AND update the flat arena in one kernel.  Returns False
+        when the subclass has no fused form for this answer (the generic decode + update then runs)."""
+        return False
+
     def _step(self, executor: Any, **kwargs: Any) -> None:
         trainer = executor
         hp = trainer.hyper_parameter
@@ -88,14 +94,17 @@ class GradientWorker(Client):
             gradient = torch.cat([g.reshape(-1) for g in real])
         self.send_data_to_server(GradientMessage(
             in_round=True, other_data={"dataset_size": trainer.dataset_size, "gradient": self._process_gradient(gradient),
-                                       "numel": gradient.numel()}))
+                                       "numel": gradient.numel(), "parity": self.__step & 1}))
         result = self._get_data_from_server()
         assert result is not None
-        d_p = self._decode_gradient(result.other_data["gradient"], gradient.numel()).to(gradient.device)
         lr = trainer.current_lr()
         if self.__momentum_buf is None or self.__momentum_buf.device != gradient.device:
             self.__momentum_buf = torch.zeros_like(gradient)
             self.__step = 0
+        if arena_order and self._apply_fused(result, flat, self.__momentum_buf, lr, hp, self.__step > 0):
+            self.__step += 1
+            return
+        d_p = self._decode_gradient(result.other_data["gradient"], gradient.numel()).to(gradient.device)
         if arena_order:
             dev = flat.device
             if self.__state is None or self.__state.device != dev:

@@ -207,6 +207,13 @@ int dls_nnadq_dequant(const uint8_t* payload, const float* scale, const float* o
 int dls_sign_pack(const float* grad, long long n, uint32_t* packed, void* stream);
 /* vote[i] = sign(sum_k sign_k[i]) in {-1,0,+1}; rows are packed sign words (1 = negative) */
 int dls_sign_majority(const uint32_t* const* rows, int n_rows, long long n, float* vote, void* stream);
+/* signSGD step in ONE launch: majority vote over n_rows packed rows (local or peer-mapped) + momentum /
+ * nesterov / p -= lr * vote on this worker's flat parameters (+ bf16 shadow: all elements, or only the tensors
+ * whose shadow_mask entry is non-zero).  No counterpart kernel in the reference (its scaffold applies the
+ * update per tensor in Python, worker/gradient_worker.py:96-116). */
+int dls_sign_vote_sgd(const uint32_t* const* rows, int n_rows, long long n, float* params, float* mom, float lr,
+                      float momentum, float dampening, int nesterov, int mom_ready, void* shadow,
+                      const uint8_t* shadow_mask, const long long* tensor_offsets, int n_tensors, void* stream);
 
 /* ---- FedDropoutAvg / FedOBD helpers (reference: method/fed_dropout_avg/worker.py:23-27,
  *      method/fed_obd/obd_algorithm.py:129-145) ---------------------------------------- */

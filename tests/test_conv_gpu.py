@@ -218,7 +218,8 @@ def test_conv_bn_act_statistics_from_epilogue(n, ci, hw, co, st, relu, res):
         y.float().square().sum().backward()  # noqa
         outs.append((y.float(), xi.grad.clone(), conv.weight.grad.clone(), bn.weight.grad.clone(), bn.bias.grad.clone()))
     for a, b in zip(*outs):  # statistics summed in a different order: bf16-level differences that backward amplifies
-        torch.testing.assert_close(a, b, rtol=5e-2, atol=1e-1 * float(b.abs().max()))
+        rel = float((a.float() - b.float()).norm() / b.float().norm().clamp_min(1e-12))
+        assert rel < 3e-2, rel
     # and against the plain fp32 statement of the op
     with torch.no_grad():
         ref = B.oracle_bn_act(torch.nn.functional.conv2d(x.bfloat16().float(), conv.weight.bfloat16().float(), None, st, 1)
