@@ -12,6 +12,8 @@ from ...server.server import Server
 
 
 class SignSGDServer(Server):
+    _one_message_per_sweep = False  # workers report per optimizer step and may be out of phase by a batch
+
     def __init__(self, **kwargs: Any) -> None:
         kwargs.pop("algorithm", None)
         super().__init__(**kwargs)

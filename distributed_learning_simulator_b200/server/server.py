@@ -106,7 +106,7 @@ class Server(Executor):
             worker_set: set = set()
             timeout = getattr(self.config, "round_timeout", None)
             while not self._stopped():
-                if not worker_set:
+                if not worker_set or not self._one_message_per_sweep:
                     worker_set = set(range(self._endpoint.worker_num))
                 assert self._endpoint.worker_num == self.config.worker_number
                 ready = self._endpoint.wait_for_data(worker_set, timeout=timeout)
@@ -121,6 +121,11 @@ class Server(Executor):
             self._endpoint.close()
             self._server_exit()
             get_logger().debug("end server")
+
+    # Aggregation protocols answer once every worker has reported, so a sweep takes exactly one message per
+    # worker.  Per-step protocols (sign_SGD) do not: a worker whose shard holds one more batch sends two
+    # messages while the others send one, and must be listened to at any time.
+    _one_message_per_sweep = True
 
     def _before_start(self) -> None:
         pass

@@ -110,3 +110,12 @@ def test_shapley_methods(monkeypatch, conf, workers):
     assert sorted(res["sv"][1]) == list(range(workers))
     with open(os.path.join(res["save_dir"], "shapley_values.json"), encoding="utf8") as f:
         assert sorted(json.load(f)) == ["1", "2"]
+
+
+def test_sign_sgd_workers_out_of_phase(monkeypatch):
+    """Shards with different batch counts: one worker keeps stepping while the others already wait for the epoch
+    acknowledgement, i.e. it sends two messages where they send one.  The server must keep listening to it."""
+    config, res = _run("sign_sgd/cifar10.yaml", monkeypatch, model_name="LeNet5", dataset_name="MNIST", worker_number=3,
+                       round=1, epoch=3, learning_rate=0.002, batch_size=64,
+                       dataset_kwargs={"train_size": 1920, "test_size": 300})
+    assert sorted(res["performance"]) == [1, 2, 3]
