@@ -112,3 +112,66 @@ def test_p2p_reduce_and_distributed_training(tmp_path, nvls, two_stage, world):
     runs = [json.load(open(tmp_path / f"train_{r}.json")) for r in range(world)]
     assert all(t["performance"] == runs[0]["performance"] and t["p2p_reductions"] == 3 for t in runs)
     assert runs[0]["performance"]["3"]["test_accuracy"] > 0.2
+
+
+STRESS = r"""
+import json, os, random, sys, time
+sys.path.insert(0, {root!r})
+import torch
+from distributed_learning_simulator_b200.parallel.context import get_context
+from distributed_learning_simulator_b200.engine.model_util import ParameterLayout
+
+ctx = get_context()
+layout = ParameterLayout(["a", "b"], [torch.Size([65536 + 123]), torch.Size([4099])])
+ctx.setup_arena(layout, worker_number=3 * ctx.world)
+n = layout.total
+rng = random.Random(1234 + ctx.rank)          # per-rank jitter, same data on every rank (seeded by round)
+noise_stream = torch.cuda.Stream(device=ctx.device)
+a = torch.randn(4096, 4096, device=ctx.device, dtype=torch.bfloat16)
+worst = 0.0
+old = torch.zeros(n, device=ctx.device)
+for rnd in range(200):
+    with torch.cuda.stream(noise_stream):      # keeps the SMs busy while the reduction's CTAs spin on peer flags
+        for _ in range(rng.randint(0, 3)):
+            a @ a
+    workers = 3 * ctx.world if rnd % 2 else ctx.world   # two-stage and direct rounds alternate
+    rows, weights, payloads = [], [], []
+    for w in range(workers):
+        g = torch.Generator(device="cuda").manual_seed(1000 * rnd + w)
+        row = torch.randn(n, device=ctx.device, generator=g)
+        rows.append(row); weights.append(float(1 + (w * 7 + rnd) % 5))
+        if ctx.is_local(w):
+            ctx.store_upload(w, row)
+    if rng.random() < 0.3:
+        time.sleep(rng.random() * 0.002)       # ranks arrive at the kernel's flag barrier at different times
+    for w in range(workers):
+        payloads.append(ctx.remote_payload(ctx.owner_of(w), ctx.slot_of(w)))
+    out = ctx.p2p_reduce(payloads, weights, old, 0.5, 1.0 / sum(weights)).flat
+    ref = 0.5 * old.double()
+    for r, wt in zip(rows, weights):
+        ref += r.double() * (wt / sum(weights))
+    worst = max(worst, float((out.double() - ref).abs().max()))
+    old = out.clone()
+ctx.finish_reductions()
+torch.cuda.synchronize()
+with open(os.path.join({out!r}, "stress_%d.json" % ctx.rank), "w") as f:
+    json.dump({{"worst": worst, "reductions": ctx.p2p_reductions, "two_stage": ctx.two_stage_reductions}}, f)
+"""
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_p2p_reduce_flag_protocol_stress(tmp_path):
+    """200 rounds on every visible GPU (up to 8): random arrival skew at the device-side flag barrier, SM-saturating
+    kernels on a second stream of every rank while the reduction's CTAs wait on peer flags, alternating one and
+    three rows per rank (direct and two-stage paths); every result is compared with an fp64 oracle."""
+    world = min(torch.cuda.device_count(), 8)
+    script = tmp_path / "stress.py"
+    script.write_text(STRESS.format(root=ROOT, out=str(tmp_path)))
+    env = dict(os.environ, DLS_OUTPUT_ROOT=str(tmp_path), DLS_NVLS="0")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), str(script)]
+    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    for r in range(world):
+        s = json.load(open(tmp_path / f"stress_{r}.json"))
+        assert s["worst"] < 1e-5 and s["reductions"] == 200 and s["two_stage"] == 100, s
