@@ -207,11 +207,26 @@ class GraphTrainStep:
         for p in params:
             p.grad = None
         torch.cuda.synchronize(self.device)
-        graph = torch.cuda.CUDAGraph()
-        own_before = runtime.launch_count()
-        # the per-device capture stream (engine/device.py)
-        with torch.cuda.graph(graph, stream=capture_stream(self.device), capture_error_mode="thread_local"):
-            self._one_step(step, x_all, y_all, n_order)
+        # A capture can be invalidated by what another role thread does on the device at the same moment (seen
+        # with dozens of workers per GPU); the step is idempotent up to the saved state, so it is simply retried.
+        for attempt in range(4):
+            graph = torch.cuda.CUDAGraph()
+            own_before = runtime.launch_count()
+            try:
+                # the per-device capture stream (engine/device.py)
+                with torch.cuda.graph(graph, stream=capture_stream(self.device), capture_error_mode="thread_local"):
+                    self._one_step(step, x_all, y_all, n_order)
+                break
+            except RuntimeError as e:
+                if attempt == 3:
+                    raise
+                from .log import get_logger
+
+                get_logger().warning("training-step capture failed (%s), retrying", str(e).splitlines()[0])
+                del graph
+                for p in params:
+                    p.grad = None
+                torch.cuda.synchronize(self.device)
         step.own_kernels = runtime.launch_count() - own_before  # own kernel nodes in one replay
         self._fill_grad_table(step)
         self.flat.copy_(saved[0])
