@@ -1,7 +1,11 @@
-"""``random_label_iid``: every part draws ``sampled_class_number`` random labels; each label's
-samples are split evenly between the parts that drew it
-(/root/reference/simulation_lib/sampler/base.py:9-46; python ``random`` is the RNG there too,
-so a run seeded through ``config.apply_global_config()`` assigns the same labels)."""
+"""``random_label_iid`` sampling: every part draws ``sampled_class_number`` distinct labels at random and the
+samples of a label are shared evenly among the parts that drew it (what /root/reference/simulation_lib/sampler/
+base.py:9-46 does; python's ``random`` is the generator there as well, so a run seeded through
+``config.apply_global_config()`` reproduces its label assignment).
+
+The reference asserts that its single draw happens to cover every label; here the draw is repeated until it
+does (a label nobody holds would silently vanish from training).
+"""
 import random
 from typing import Any
 
@@ -9,28 +13,34 @@ from ..engine.dataset import ClassificationDatasetCollection, DatasetCollection,
 from ..engine.log import get_logger
 from ..engine.ml_type import MachineLearningPhase
 
+_MAX_DRAWS = 1000
+
+
+def draw_label_assignment(labels: list, part_number: int, labels_per_part: int) -> list[list]:
+    """``part_number`` label subsets of size ``labels_per_part`` whose union is ``labels``."""
+    if not 0 < labels_per_part < len(labels):
+        raise ValueError("sampled_class_number must be positive and smaller than the number of labels")
+    for _ in range(_MAX_DRAWS):
+        assignment = [random.sample(labels, labels_per_part) for _ in range(part_number)]
+        if set().union(*assignment) == set(labels):
+            return assignment
+    raise RuntimeError(f"{part_number} parts of {labels_per_part} labels never covered all {len(labels)} labels")
+
 
 class RandomLabelIIDSplit(DatasetCollectionSampler):
     def __init__(self, dataset_collection: DatasetCollection, part_number: int, sampled_class_number: int,
                  **kwargs: Any) -> None:
         super().__init__(dataset_collection=dataset_collection, part_number=part_number, **kwargs)
-        assert isinstance(dataset_collection, ClassificationDatasetCollection)
-        assert not dataset_collection.is_mutilabel()
-        labels = sorted(dataset_collection.get_labels())
-        assert sampled_class_number < len(labels)
-        for _ in range(1000):
-            assigned_labels = [random.sample(labels, sampled_class_number) for _ in range(part_number)]
-            if len(labels) == len(set(sum(assigned_labels, start=[]))):
-                break
-        # Assure that all labels are allocated (the reference asserts on the first draw)
-        assert len(labels) == len(set(sum(assigned_labels, start=[]))), "some label was assigned to nobody"
-        self.assigned_labels = assigned_labels
+        if not isinstance(dataset_collection, ClassificationDatasetCollection) or dataset_collection.is_mutilabel():
+            raise TypeError("random_label_iid needs a single-label classification dataset")
+        self.assigned_labels = draw_label_assignment(sorted(dataset_collection.get_labels()), part_number,
+                                                     sampled_class_number)
+        equal_weights = [{label: 1 for label in part} for part in self.assigned_labels]
         for phase in MachineLearningPhase:
-            if phase not in self._samplers:
-                continue
-            self._dataset_indices[phase] = dict(enumerate(self._samplers[phase].split_indices(
-                parts=[{label: 1 for label in part} for part in assigned_labels])))
-        for worker_id, part in enumerate(assigned_labels):
+            if phase in self._samplers:
+                split = self._samplers[phase].split_indices(parts=equal_weights)
+                self._dataset_indices[phase] = dict(enumerate(split))
+        training = self._dataset_indices[MachineLearningPhase.Training]
+        for worker_id, part in enumerate(self.assigned_labels):
             get_logger().info("worker %s has assigned labels %s", worker_id, part)
-            get_logger().info("worker %s has training set size %s", worker_id,
-                              len(self._dataset_indices[MachineLearningPhase.Training][worker_id]))
+            get_logger().info("worker %s has training set size %s", worker_id, len(training[worker_id]))
