@@ -1,56 +1,66 @@
-"""Read back a finished run from its session directory.
+"""Reading a finished run back from disk.
 
-Same contract as /root/reference/simulation_lib/analysis/session.py:9-63: point ``Session`` at
-``<save_dir>/server``; it loads ``round_record.json`` and ``config.pkl`` and walks ``..`` for
-``worker*`` directories (``hyper_parameter.pk``; ``GraphSession`` also reads
-``graph_worker_stat.json``)."""
-import functools
+A run leaves ``<save_dir>/server/{round_record.json, config.pkl}`` and one ``<save_dir>/worker_<i>/`` per worker
+(``hyper_parameter.pk``; graph workers also ``graph_worker_stat.json``).  ``Session(<save_dir>/server)`` and
+``GraphSession`` expose them the way /root/reference/simulation_lib/analysis/session.py:9-63 does
+(``round_record``, ``config``, ``worker_data``, ``rounds``, ``last_round``, ``last_test_acc``,
+``mean_test_acc``)."""
 import json
 import os
 import pickle
+from typing import Any, Callable, Iterator
 
 import dill
 
 
+def _read(path: str, mode: str, loader: Callable) -> Any:
+    with open(path, mode, **({"encoding": "utf8"} if "t" in mode else {})) as f:
+        return loader(f)
+
+
 class Session:
+    worker_file = "hyper_parameter.pk"
+
     def __init__(self, session_dir: str) -> None:
         self.session_dir = session_dir
-        with open(os.path.join(session_dir, "round_record.json"), "rt", encoding="utf8") as f:
-            self.round_record = {int(k): v for k, v in json.load(f).items()}
-        with open(os.path.join(session_dir, "config.pkl"), "rb") as f:
-            self.config = pickle.load(f)
-        self.worker_data: dict = {}
-        for name, path in self._worker_dirs():
-            with open(os.path.join(path, "hyper_parameter.pk"), "rb") as f:
-                self.worker_data[name] = {"hyper_parameter": dill.load(f)}
+        records = _read(os.path.join(session_dir, "round_record.json"), "rt", json.load)
+        self.round_record = {int(round_key): stat for round_key, stat in records.items()}
+        self.config = _read(os.path.join(session_dir, "config.pkl"), "rb", pickle.load)
+        self.worker_data: dict = {name: self._load_worker(path) for name, path in self._worker_dirs()}
         if not self.worker_data:
             raise RuntimeError(f"no worker directories next to {session_dir}")
 
-    def _worker_dirs(self) -> list[tuple[str, str]]:
-        parent = os.path.normpath(os.path.join(self.session_dir, ".."))
-        return sorted((name, os.path.join(parent, name)) for name in os.listdir(parent)
-                      if name.startswith("worker") and os.path.isdir(os.path.join(parent, name)))
+    def _worker_dirs(self) -> Iterator[tuple[str, str]]:
+        run_dir = os.path.normpath(os.path.join(self.session_dir, os.pardir))
+        for entry in sorted(os.listdir(run_dir)):
+            path = os.path.join(run_dir, entry)
+            if entry.startswith("worker") and os.path.isdir(path):
+                yield entry, path
 
-    @functools.cached_property
+    def _load_worker(self, path: str) -> dict:
+        return {"hyper_parameter": _read(os.path.join(path, self.worker_file), "rb", dill.load)}
+
+    # ---- derived views -------------------------------------------------------------------------------------
+    @property
     def rounds(self) -> list:
-        return sorted(self.round_record.keys())
+        return sorted(self.round_record)
 
-    @functools.cached_property
+    @property
     def last_round(self) -> int:
-        return self.rounds[-1]
+        return max(self.round_record)
 
-    @functools.cached_property
+    @property
     def last_test_acc(self) -> float:
         return self.round_record[self.last_round]["test_accuracy"]
 
-    @functools.cached_property
+    @property
     def mean_test_acc(self) -> float:
-        return sum(r["test_accuracy"] for r in self.round_record.values()) / len(self.round_record)
+        accuracies = [stat["test_accuracy"] for stat in self.round_record.values()]
+        return sum(accuracies) / len(accuracies)
 
 
 class GraphSession(Session):
-    def __init__(self, session_dir: str) -> None:
-        super().__init__(session_dir=session_dir)
-        for name, path in self._worker_dirs():
-            with open(os.path.join(path, "graph_worker_stat.json"), "rt", encoding="utf8") as f:
-                self.worker_data[name] = json.load(f)
+    worker_file = "graph_worker_stat.json"
+
+    def _load_worker(self, path: str) -> dict:
+        return _read(os.path.join(path, self.worker_file), "rt", json.load)
