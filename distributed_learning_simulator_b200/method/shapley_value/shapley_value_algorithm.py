@@ -1,37 +1,53 @@
-"""FedAvg that also computes per-round Shapley values of the workers.
+"""FedAvg that also attributes each round's gain to the workers (Shapley values).
 
-Behaviour of /root/reference/simulation_lib/method/shapley_value/shapley_value_algorithm.py:
-11-92: ``accumulate=False`` (every worker's full model is kept), metric ``accuracy``, the
-engine is created lazily at round 1 with ``last_round_metric = stat[0].test_accuracy``,
-``shapley_values[round]`` / ``shapley_values_S[round]`` snapshots, optional
-``choose_best_subset`` aggregation, ``shapley_values.json`` (+``_S``) written on exit.
+What /root/reference/simulation_lib/method/shapley_value/shapley_value_algorithm.py:11-92 provides is kept:
+every worker's full model is retained (``accumulate=False``), the utility of a coalition is the test
+``accuracy`` of the dataset-size-weighted average of its members, the engine is created at round 1 from the
+round-0 test metric, ``shapley_values[round]`` / ``shapley_values_S[round]`` are recorded, ``choose_best_subset``
+restricts the round's aggregate to the best coalition, and ``exit`` writes ``shapley_values.json`` (+ ``_S``).
 
-The utility of a coalition is the test accuracy of the dataset-size-weighted average of
-its members' models (:67-76).  The reference builds that average on the CPU and runs one
-full test inference per coalition, strictly sequentially.  Here the N uploaded models are
-``[P]`` rows in HBM; a coalition model is one launch of the fused reduce kernel, and when
-the tester model is supported by ``ops.subset_eval`` many coalitions are evaluated in one
-batched launch (the engines call ``prefetch``).
+How a utility is computed is this framework's own: the uploads are ``[P]`` rows in HBM, a coalition model is one
+launch of the fused reduce kernel, and when ``ops.subset_eval`` supports the tester model many coalitions are
+evaluated per launch -- the engines ask for whole batches through ``set_batch_metric_function``.
 """
-import copy
 import json
 import os
 from typing import Any, Iterable, Type
 
 from ...algorithm.shapley_value import GTGShapleyValue, HierarchicalShapleyValue, MultiRoundShapleyValue
 from ...engine.log import get_logger
-from ..common_import import AggregationServer, FedAVGAlgorithm, Message
 from ...utils import tracing
+from ..common_import import AggregationServer, FedAVGAlgorithm, Message
+
+
+class _CoalitionUtility:
+    """v(S) for the uploads of the current round."""
+
+    def __init__(self, server: AggregationServer, uploads: dict, metric_type: str) -> None:
+        self.server, self.uploads, self.metric_type = server, uploads, metric_type
+
+    def __call__(self, subset: Iterable) -> float:
+        members = set(subset)
+        if not members:
+            raise ValueError("the empty coalition has no model")
+        model = FedAVGAlgorithm._aggregate_worker_data({w: m for w, m in self.uploads.items() if w in members})
+        return self.server.get_metric(model, keep_performance_logger=False)[self.metric_type]
+
+    def batched(self) -> Any:
+        """A callable that evaluates a list of coalitions in one launch, or None when the model has no batched path."""
+        from ...ops import subset_eval
+
+        return subset_eval.make_batch_evaluator(self.server, self.uploads, self.metric_type)
 
 
 class ShapleyValueAlgorithm(FedAVGAlgorithm):
     def __init__(self, sv_algorithm_cls: Type, server: AggregationServer, **kwargs: Any) -> None:
         super().__init__(**kwargs)
-        self._server: AggregationServer = server
-        self.accumulate = False
-        self.metric_type: str = "accuracy"
-        self.sv_algorithm: Any = None
+        self.accumulate = False          # coalitions need every worker's own model
+        self.metric_type = "accuracy"
+        self._server = server
         self.sv_algorithm_cls = sv_algorithm_cls
+        self.sv_algorithm: Any = None
         self.shapley_values: dict = {}
         self.shapley_values_S: dict = {}
         self.subset_evaluations = 0
@@ -42,70 +58,65 @@ class ShapleyValueAlgorithm(FedAVGAlgorithm):
 
     @property
     def choose_best_subset(self) -> bool:
-        return self.config.algorithm_kwargs.get("choose_best_subset", False)
+        return bool(self.config.algorithm_kwargs.get("choose_best_subset", False))
 
+    # ---- engine ------------------------------------------------------------------------------------------
     def _get_players(self) -> Iterable:
-        return sorted(self._all_worker_data.keys())
+        return sorted(self._all_worker_data)
 
     def _engine_kwargs(self) -> dict:
-        kwargs = {"seed": self.config.reproducible_env_config.seed}
+        options = {"seed": self.config.reproducible_env_config.seed}
         if "speculative_prefetch" in self.config.algorithm_kwargs:
-            kwargs["speculative_prefetch"] = bool(self.config.algorithm_kwargs["speculative_prefetch"])
-        return kwargs
+            options["speculative_prefetch"] = bool(self.config.algorithm_kwargs["speculative_prefetch"])
+        return options
 
-    def aggregate_worker_data(self) -> Message:
+    def __engine(self) -> Any:
         if self.sv_algorithm is None:
-            assert self._server.round_number == 1
-            self.sv_algorithm = self.sv_algorithm_cls(
-                players=self._get_players(),
-                last_round_metric=self._server.performance_stat[self._server.round_number - 1][
-                    f"test_{self.metric_type}"],
-                **self._engine_kwargs(),
-            )
-        assert self.sv_algorithm is not None
-        self.sv_algorithm.set_metric_function(self._get_subset_metric)
-        self.sv_algorithm.set_batch_metric_function(self._batch_evaluator())
-        with tracing.phase("shapley"):
-            self.sv_algorithm.compute(round_number=self._server.round_number)
-        self.subset_evaluations += self.sv_algorithm.evaluations
-        self.sv_algorithm.evaluations = 0
-        self.shapley_values[self._server.round_number] = copy.deepcopy(
-            self._convert_shapley_values(self.sv_algorithm.shapley_values))
-        self.shapley_values_S[self._server.round_number] = self._convert_shapley_values(
-            self.sv_algorithm.shapley_values_S)
-        if self.choose_best_subset:
-            best_subset: set = set(self.shapley_values_S[self._server.round_number].keys())
-            if best_subset:
-                get_logger().warning("use subset %s", best_subset)
-                self._all_worker_data = {k: v for k, v in self._all_worker_data.items() if k in best_subset}
-        return super().aggregate_worker_data()
+            round_number = self._server.round_number
+            if round_number != 1:
+                raise RuntimeError("the Shapley engine starts at round 1 (it needs the round-0 metric)")
+            baseline = self._server.performance_stat[round_number - 1][f"test_{self.metric_type}"]
+            self.sv_algorithm = self.sv_algorithm_cls(players=self._get_players(), last_round_metric=baseline,
+                                                      **self._engine_kwargs())
+        return self.sv_algorithm
 
     def _convert_shapley_values(self, shapley_values: dict) -> dict:
         return dict(shapley_values)
 
+    # ---- one round ---------------------------------------------------------------------------------------
+    def aggregate_worker_data(self) -> Message:
+        engine = self.__engine()
+        round_number = self._server.round_number
+        utility = _CoalitionUtility(self._server, self._all_worker_data, self.metric_type)
+        engine.set_metric_function(utility)
+        engine.set_batch_metric_function(utility.batched())
+        with tracing.phase("shapley"):
+            engine.compute(round_number=round_number)
+        self.subset_evaluations += engine.evaluations
+        engine.evaluations = 0
+        self.shapley_values[round_number] = self._convert_shapley_values(engine.shapley_values)
+        self.shapley_values_S[round_number] = self._convert_shapley_values(engine.shapley_values_S)
+        best = set(self.shapley_values_S[round_number]) if self.choose_best_subset else set()
+        if best:
+            get_logger().warning("use subset %s", best)
+            self._all_worker_data = {w: m for w, m in self._all_worker_data.items() if w in best}
+        return super().aggregate_worker_data()
+
+    # kept for subclasses / callers that evaluate a coalition directly
     def _get_subset_metric(self, subset: Iterable) -> float:
-        assert subset
-        members = set(subset)
-        worker_data = FedAVGAlgorithm._aggregate_worker_data(
-            {k: v for k, v in self._all_worker_data.items() if k in members})
-        assert worker_data
-        return self._server.get_metric(worker_data, keep_performance_logger=False)[self.metric_type]
-
-    def _batch_evaluator(self) -> Any:
-        """A callable evaluating a list of coalitions in one launch, or None."""
-        from ...ops import subset_eval
-
-        return subset_eval.make_batch_evaluator(self._server, self._all_worker_data, self.metric_type)
+        return _CoalitionUtility(self._server, self._all_worker_data, self.metric_type)(subset)
 
     def exit(self) -> None:
         if self.sv_algorithm is None:
             return
-        os.makedirs(self.config.save_dir, exist_ok=True)
-        with open(os.path.join(self.config.save_dir, "shapley_values.json"), "wt", encoding="utf8") as f:
-            json.dump(self.shapley_values, f)
+        out_dir = self.config.save_dir
+        os.makedirs(out_dir, exist_ok=True)
+        outputs = {"shapley_values.json": self.shapley_values}
         if self.choose_best_subset:
-            with open(os.path.join(self.config.save_dir, "shapley_values_S.json"), "wt", encoding="utf8") as f:
-                json.dump(self.shapley_values_S, f)
+            outputs["shapley_values_S.json"] = self.shapley_values_S
+        for name, table in outputs.items():
+            with open(os.path.join(out_dir, name), "wt", encoding="utf8") as f:
+                json.dump(table, f)
 
 
 class GTGShapleyValueAlgorithm(ShapleyValueAlgorithm):
@@ -123,5 +134,5 @@ class HierarchicalShapleyValueAlgorithm(ShapleyValueAlgorithm):
         super().__init__(HierarchicalShapleyValue, *args, **kwargs)
 
     def _engine_kwargs(self) -> dict:
-        kw = self.config.algorithm_kwargs
-        return {"part_number": kw.get("part_number", 2), "vp_size": kw.get("vp_size")}
+        options = self.config.algorithm_kwargs
+        return {"part_number": options.get("part_number", 2), "vp_size": options.get("vp_size")}
