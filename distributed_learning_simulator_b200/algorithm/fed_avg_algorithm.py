@@ -24,6 +24,39 @@ from ..message import Message, ParameterMessage
 from .aggregation_algorithm import AggregationAlgorithm
 
 
+class _StreamingSum:
+    """fp64 running sums ``sum_w weight_w * value_w`` and ``sum_w weight_w`` per tensor name -- the fallback for
+    uploads the fused kernel does not take (CPU tensors, custom weights, partial dicts).  A worker's tensors can
+    be dropped as soon as they have been added."""
+
+    def __init__(self) -> None:
+        self.weighted: TensorDict = {}
+        self.weights: dict[str, Any] = {}
+        self.dtypes: dict[str, Any] = {}
+
+    def __bool__(self) -> bool:
+        return bool(self.weighted)
+
+    def add(self, name: str, value: torch.Tensor, weight: Any) -> None:
+        self.dtypes[name] = value.dtype
+        term = value.to(dtype=torch.float64) * weight
+        if name in self.weighted:
+            self.weighted[name] += term
+            self.weights[name] = self.weights[name] + weight
+        else:
+            self.weighted[name] = term
+            self.weights[name] = weight
+
+    def finish(self, normalise: Any) -> TensorDict:
+        """``normalise(name, weighted_sum, total_weight)`` per tensor, cast back to the upload dtype."""
+        result = {name: normalise(name, total, self.weights[name]).to(dtype=self.dtypes[name])
+                  for name, total in self.weighted.items()}
+        self.__init__()
+        if bool(torch.stack([t.isnan().any() for t in result.values()]).any()):
+            raise AssertionError("NaN in aggregated parameters")
+        return result
+
+
 class FedAVGAlgorithm(AggregationAlgorithm):
     # subclasses that change _get_weight/_apply_total_weight set this to the name of the
     # fused-kernel variant implementing the same maths, or None for "no fused path"
@@ -32,11 +65,9 @@ class FedAVGAlgorithm(AggregationAlgorithm):
     def __init__(self) -> None:
         super().__init__()
         self.accumulate: bool = True
-        self.__dtypes: dict[str, Any] = {}
-        self.__total_weights: dict[str, Any] = {}
-        self.__parameter: TensorDict = {}
-        self.__pending: dict[int, Message] = {}   # raw uploads kept for the fused kernel
         self.use_fused: bool = True
+        self.__streamed = _StreamingSum()
+        self.__pending: dict[int, Message] = {}   # raw uploads kept for the fused kernel
 
     # ---- upload handling -------------------------------------------------------------
     def process_worker_data(self, worker_id: int, worker_data: Message | None,
@@ -44,55 +75,35 @@ class FedAVGAlgorithm(AggregationAlgorithm):
         if worker_data is None:
             self._skipped_workers.add(worker_id)
             return
-        self._old_parameter_dict = old_parameter_dict
-        if self.accumulate and self.use_fused and self.fused_variant is not None:
-            from ..ops import reduce as reduce_ops
-
-            # only while nothing went down the streaming path this round: the two accumulators are
-            # never live together (a fusable upload after a non-fusable one is streamed as well)
-            if not self.__parameter and reduce_ops.can_fuse(worker_data, old_parameter_dict):
-                # defer: the kernel consumes the raw (possibly delta / packed) rows
-                self.__pending[worker_id] = worker_data
-                self._all_worker_data[worker_id] = worker_data
-                return
-        self.__flush_pending()
         from ..ops import reduce as reduce_ops
 
-        worker_data = reduce_ops.materialize(worker_data)  # arena / packed payloads -> local tensors
-        worker_data = self._process_worker_data(worker_data=worker_data, old_parameter_dict=old_parameter_dict)
-        self._all_worker_data[worker_id] = worker_data
-        if not self.accumulate or not isinstance(worker_data, ParameterMessage):
+        self._old_parameter_dict = old_parameter_dict
+        fusable = self.accumulate and self.use_fused and self.fused_variant is not None
+        # the two accumulators are never live together: once something has been streamed this round, every later
+        # upload is streamed as well (and deferred rows are folded in the moment a non-fusable upload arrives)
+        if fusable and not self.__streamed and reduce_ops.can_fuse(worker_data, old_parameter_dict):
+            self.__pending[worker_id] = worker_data   # the kernel consumes the raw (delta / packed) row
+            self._all_worker_data[worker_id] = worker_data
             return
-        self.__accumulate(worker_data)
-        # release to reduce memory pressure
-        worker_data.parameter = {}
+        self.__stream_pending()
+        self.__stream(worker_id, worker_data)
 
-    def __accumulate(self, worker_data: ParameterMessage) -> None:
-        for k, v in worker_data.parameter.items():
-            self.__dtypes[k] = v.dtype
-            weight = self._get_weight(dataset_size=worker_data.dataset_size, name=k, parameter=v)
-            tmp = v.to(dtype=torch.float64) * weight
-            if k not in self.__parameter:
-                self.__parameter[k] = tmp
-            else:
-                self.__parameter[k] += tmp
-            if k not in self.__total_weights:
-                self.__total_weights[k] = weight
-            else:
-                self.__total_weights[k] = self.__total_weights[k] + weight
+    def __stream(self, worker_id: int, raw: Message) -> None:
+        from ..ops import reduce as reduce_ops
 
-    def __flush_pending(self) -> None:
-        """A non-fusable upload arrived: fold deferred rows into the streaming accumulators."""
+        upload = self._process_worker_data(worker_data=reduce_ops.materialize(raw),
+                                           old_parameter_dict=self._old_parameter_dict)
+        self._all_worker_data[worker_id] = upload
+        if self.accumulate and isinstance(upload, ParameterMessage):
+            for name, value in upload.parameter.items():
+                self.__streamed.add(name, value, self._get_weight(dataset_size=upload.dataset_size, name=name,
+                                                                  parameter=value))
+            upload.parameter = {}   # the sums hold everything that is needed: free the worker's copy
+
+    def __stream_pending(self) -> None:
         pending, self.__pending = self.__pending, {}
         for worker_id, raw in pending.items():
-            from ..ops import reduce as reduce_ops
-
-            raw = reduce_ops.materialize(raw)
-            msg = self._process_worker_data(worker_data=raw, old_parameter_dict=self._old_parameter_dict)
-            self._all_worker_data[worker_id] = msg
-            if isinstance(msg, ParameterMessage):
-                self.__accumulate(msg)
-                msg.parameter = {}
+            self.__stream(worker_id, raw)
 
     def _get_weight(self, dataset_size: int, name: str, parameter: Any) -> Any:
         assert dataset_size != 0
@@ -111,15 +122,9 @@ class FedAVGAlgorithm(AggregationAlgorithm):
             pending, self.__pending = self.__pending, {}
             parameter = reduce_ops.fused_aggregate(pending, self._old_parameter_dict, variant=self.fused_variant)
         else:
-            assert self.__parameter
-            parameter = self.__parameter
-            self.__parameter = {}
-            for k, v in parameter.items():
-                parameter[k] = self._apply_total_weight(
-                    name=k, parameter=v, total_weight=self.__total_weights[k]).to(dtype=self.__dtypes[k])
-            nan = torch.stack([p.isnan().any() for p in parameter.values()]).any()
-            assert not bool(nan), "NaN in aggregated parameters"
-            self.__total_weights = {}
+            assert self.__streamed, "no upload to aggregate"
+            parameter = self.__streamed.finish(
+                lambda name, total, weight: self._apply_total_weight(name=name, parameter=total, total_weight=weight))
         return ParameterMessage(
             parameter=parameter,
             end_training=next(iter(self._all_worker_data.values())).end_training,
@@ -129,8 +134,7 @@ class FedAVGAlgorithm(AggregationAlgorithm):
     def clear_worker_data(self) -> None:
         super().clear_worker_data()
         self.__pending = {}
-        self.__parameter = {}
-        self.__total_weights = {}
+        self.__streamed = _StreamingSum()
 
     @classmethod
     def _aggregate_worker_data(cls, all_worker_data: dict[int, ParameterMessage]) -> ParameterMessage:
