@@ -76,26 +76,41 @@ sq_pack_kernel(const float* __restrict__ flat, long long n, const long long* __r
     for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < n_groups;
          g += (long long)gridDim.x * blockDim.x) {
         const long long i0 = g << 3;
+        // one Philox call per group: eight 16-bit uniforms (the rounding probability is resolved to 2^-16)
         const uint4 r0 = philox4x32((uint32_t)g, (uint32_t)(g >> 32), 0u, 0u, (uint32_t)seed, (uint32_t)(seed >> 32));
-        const uint4 r1 = philox4x32((uint32_t)g, (uint32_t)(g >> 32), 1u, 0u, (uint32_t)seed, (uint32_t)(seed >> 32));
-        const uint32_t rnd[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+        const uint32_t raw[4] = {r0.x, r0.y, r0.z, r0.w};
         int t = find_segment(s_off, n_tensors, i0);
         uint32_t sign = 0;
         uint8_t q[8];
+        if (i0 + 8 <= s_off[t + 1]) {
+            // the whole group lies inside one tensor (all but a handful do): two 128-bit loads, one scale
+            const float4 a = ld_stream_f4(flat + i0), b = ld_stream_f4(flat + i0 + 4);
+            const float x[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+            const float s = __uint_as_float(absmax_bits[t]);
+            const float inv = s > 0.f ? (float)level / s : 0.f;
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            const long long i = i0 + e;
-            q[e] = 0;
-            if (i < n) {
-                while (i >= s_off[t + 1]) ++t;
-                const float x = flat[i];
-                const float s = __uint_as_float(absmax_bits[t]);
-                float y = s > 0.f ? __fdiv_rn(fabsf(x), s) * (float)level : 0.f;
+            for (int e = 0; e < 8; ++e) {
+                const float y = fminf(fabsf(x[e]) * inv, (float)level);
                 const float lo = floorf(y);
-                float qq = lo + ((u32_to_unit(rnd[e]) < (y - lo)) ? 1.f : 0.f);
-                qq = fminf(qq, (float)level);
-                q[e] = (uint8_t)qq;
-                sign |= (x < 0.f ? 1u : 0u) << e;
+                const float u = (float)((raw[e >> 1] >> ((e & 1) * 16)) & 0xFFFFu) * (1.0f / 65536.0f);
+                q[e] = (uint8_t)fminf(lo + (u < (y - lo) ? 1.f : 0.f), (float)level);
+                sign |= (x[e] < 0.f ? 1u : 0u) << e;
+            }
+        } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const long long i = i0 + e;
+                q[e] = 0;
+                if (i < n) {
+                    while (i >= s_off[t + 1]) ++t;
+                    const float xv = flat[i];
+                    const float s = __uint_as_float(absmax_bits[t]);
+                    const float y = s > 0.f ? fminf(__fdiv_rn(fabsf(xv), s) * (float)level, (float)level) : 0.f;
+                    const float lo = floorf(y);
+                    const float u = (float)((raw[e >> 1] >> ((e & 1) * 16)) & 0xFFFFu) * (1.0f / 65536.0f);
+                    q[e] = (uint8_t)fminf(lo + (u < (y - lo) ? 1.f : 0.f), (float)level);
+                    sign |= (xv < 0.f ? 1u : 0u) << e;
+                }
             }
         }
         if (i0 + 8 <= n) {
@@ -123,6 +138,20 @@ sq_dequant_kernel(const uint8_t* __restrict__ payload, const uint8_t* __restrict
         const long long i0 = g << 3;
         const uint32_t sign = sign_plane[g];
         int t = find_segment(s_off, n_tensors, i0);
+        if (i0 + 8 <= s_off[t + 1]) {
+            // one 64-bit load of the eight codes, two 128-bit stores
+            const uint2 w = *reinterpret_cast<const uint2*>(payload + i0);
+            const float sc = scale[t];
+            float v[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const float m = (float)(((e < 4 ? w.x : w.y) >> ((e & 3) * 8)) & 0xFFu) * sc;
+                v[e] = ((sign >> e) & 1u) ? -m : m;
+            }
+            st_stream_f4(out + i0, make_float4(v[0], v[1], v[2], v[3]));
+            st_stream_f4(out + i0 + 4, make_float4(v[4], v[5], v[6], v[7]));
+            continue;
+        }
         for (int e = 0; e < 8 && i0 + e < n; ++e) {
             const long long i = i0 + e;
             while (i >= s_off[t + 1]) ++t;

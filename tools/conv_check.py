@@ -184,6 +184,10 @@ def main() -> None:
     timing = "--time" in sys.argv
     kind = args[0] if args else "all"
     if kind == "all":
+        from distributed_learning_simulator_b200.utils.clocks import ClockSampler
+
+        sampler = ClockSampler(gpu_index=0)
+        sampler.start()
         for k in ("fprop", "dgrad", "wgrad", "direct"):
             cmd = [sys.executable, os.path.abspath(__file__), k] + (["--time"] if timing else [])
             res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
@@ -191,6 +195,7 @@ def main() -> None:
             print(res.stdout[-6000:])
             if res.returncode != 0:
                 print(res.stderr[-3000:])
+        print(json.dumps({"clocks": sampler.stop()}))
         return
     if kind == "direct":
         run_direct(timing)

@@ -18,7 +18,11 @@ from distributed_learning_simulator_b200.ops import quant as Q  # noqa: E402
 from distributed_learning_simulator_b200.ops import reduce as R  # noqa: E402
 from distributed_learning_simulator_b200.ops import sgd as S  # noqa: E402
 
+from distributed_learning_simulator_b200.utils.clocks import ClockSampler  # noqa: E402
+
 dev = torch.device("cuda", 0)
+_clock_sampler = ClockSampler(gpu_index=0)
+_clock_sampler.start()
 REPS = int(os.environ.get("REPS", "20"))
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > L2 (126 MB)
 results = {}
@@ -151,6 +155,8 @@ for (name, m, n, k, off) in [("fc1", 5000, 120, 400, 2572), ("conv2", 5000 * 100
 
     timed(f"materialise + gemm {name} S={S_} NW={NW} {m}x{n}x{k}", two_step, flops=2.0 * S_ * m * n * k, cold=False)
 
+results["clocks"] = _clock_sampler.stop()  # SM clock / throttle record of this run
+print("clocks", results["clocks"], flush=True)
 out_path = os.environ.get("OUT", "gpurun_out/kernel_times.json")
 os.makedirs(os.path.dirname(out_path), exist_ok=True)
 with open(out_path, "w") as f:
