@@ -15,6 +15,7 @@ OBJ_DIR = os.path.join(LIB_DIR, "obj")
 LIB_PATH = os.path.join(LIB_DIR, "libdls_b200.so")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
+NVCC_FLAGS += os.environ.get("DLS_NVCC_EXTRA", "").split()  # e.g. -DDLS_CONV_TIMELINE for tools/conv_timeline.py
 
 
 def find_nvcc() -> str:

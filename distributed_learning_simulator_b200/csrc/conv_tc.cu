@@ -39,6 +39,9 @@ namespace dls {
 constexpr int kConvMaxTaps = 36;
 constexpr int kConvMaxClasses = 4;
 constexpr int kConvThreads = 192;
+// fprop / dgrad kernels: 8 epilogue warps (two per tensor-memory lane quarter, each taking every other 32-column
+// chunk) -- a lone warp per scheduler cannot hide the latencies of the convert / store / statistics chain
+constexpr int kConvWideThreads = 320;
 
 struct ConvTap {
     int16_t dh, dw;     // shift of the box origin in the (parity-view) h / w coordinates
@@ -107,63 +110,87 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32])
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// column sums over the warp's 32 rows: butterfly that halves the value count per step, lane l ends with the
+// totals of column l
+__device__ __forceinline__ void conv_chunk_stats(const float (&v)[32], bool row_ok, int col0, int n_out,
+                                                 float* __restrict__ stats, int lane) {
+    float s1[32], s2[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        const float x = row_ok ? v[j] : 0.f;
+        s1[j] = x;
+        s2[j] = x * x;
+    }
+#pragma unroll
+    for (int step = 16; step >= 1; step >>= 1) {
+        const bool upper = (lane & step) != 0;
+#pragma unroll
+        for (int j = 0; j < step; ++j) {
+            // keep columns [j + (upper ? step : 0)], send the other half to the partner lane
+            const float keep1 = upper ? s1[j + step] : s1[j];
+            const float send1 = upper ? s1[j] : s1[j + step];
+            const float keep2 = upper ? s2[j + step] : s2[j];
+            const float send2 = upper ? s2[j] : s2[j + step];
+            s1[j] = keep1 + __shfl_xor_sync(0xffffffffu, send1, step);
+            s2[j] = keep2 + __shfl_xor_sync(0xffffffffu, send2, step);
+        }
+    }
+    if (col0 + lane < n_out) {
+        atomicAdd(stats + col0 + lane, s1[0]);
+        atomicAdd(stats + n_out + col0 + lane, s2[0]);
+    }
+}
+
 // Epilogue of one 32-column chunk of an output row (one thread = one pixel row of the tile): bias, rounding to
 // the stored bf16, 128-bit stores, and -- when `stats` is given -- per-channel sum / sum of squares over the
 // warp's 32 rows added to stats[0][c], stats[1][c] (the BatchNorm that follows needs no reduction pass).
 __device__ __forceinline__ void conv_store_chunk(float (&v)[32], bool row_ok, __nv_bfloat16* dst_row, int col0,
                                                  int n_out, const float* __restrict__ bias, float* __restrict__ stats,
                                                  int lane) {
+    __nv_bfloat16* dst = dst_row + col0;
+    if (col0 + 32 <= n_out && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+        // whole chunk, 16-byte aligned row: the common case, kept free of per-column predicates
+        if (bias != nullptr) {
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const float4 b = __ldg(reinterpret_cast<const float4*>(bias + col0) + q);
+                v[4 * q] += b.x; v[4 * q + 1] += b.y; v[4 * q + 2] += b.z; v[4 * q + 3] += b.w;
+            }
+        }
+        uint32_t packed[16];
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+            const __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * e], v[2 * e + 1]);
+            packed[e] = *reinterpret_cast<const uint32_t*>(&h);
+        }
+        if (row_ok) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                reinterpret_cast<uint4*>(dst)[q] =
+                    make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
+        }
+        if (stats != nullptr) {
+            // statistics and consumers see the value that is stored: widen the packed bf16 back (a shift / a mask)
+#pragma unroll
+            for (int e = 0; e < 16; ++e) {
+                v[2 * e] = __uint_as_float(packed[e] << 16);
+                v[2 * e + 1] = __uint_as_float(packed[e] & 0xffff0000u);
+            }
+            conv_chunk_stats(v, row_ok, col0, n_out, stats, lane);
+        }
+        return;
+    }
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
         if (bias != nullptr && col0 + j < n_out) v[j] += bias[col0 + j];
-        v[j] = __bfloat162float(__float2bfloat16(v[j]));  // statistics and consumers see the value that is stored
+        v[j] = __bfloat162float(__float2bfloat16(v[j]));
     }
     if (row_ok) {
-        __nv_bfloat16* dst = dst_row + col0;
-        if (col0 + 32 <= n_out && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                uint4 pk;
-                __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&pk);
-#pragma unroll
-                for (int e = 0; e < 4; ++e) hh[e] = __floats2bfloat162_rn(v[8 * q + 2 * e], v[8 * q + 2 * e + 1]);
-                reinterpret_cast<uint4*>(dst)[q] = pk;
-            }
-        } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-                if (col0 + j < n_out) dst[j] = __float2bfloat16(v[j]);
-        }
+        for (int j = 0; j < 32; ++j)
+            if (col0 + j < n_out) dst[j] = __float2bfloat16(v[j]);
     }
-    if (stats != nullptr) {
-        // column sums over the warp's 32 rows: butterfly that halves the value count per step, lane l ends
-        // with the totals of column l
-        float s1[32], s2[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            const float x = row_ok ? v[j] : 0.f;
-            s1[j] = x;
-            s2[j] = x * x;
-        }
-#pragma unroll
-        for (int step = 16; step >= 1; step >>= 1) {
-            const bool upper = (lane & step) != 0;
-#pragma unroll
-            for (int j = 0; j < step; ++j) {
-                // keep columns [j + (upper ? step : 0)], send the other half to the partner lane
-                const float keep1 = upper ? s1[j + step] : s1[j];
-                const float send1 = upper ? s1[j] : s1[j + step];
-                const float keep2 = upper ? s2[j + step] : s2[j];
-                const float send2 = upper ? s2[j] : s2[j + step];
-                s1[j] = keep1 + __shfl_xor_sync(0xffffffffu, send1, step);
-                s2[j] = keep2 + __shfl_xor_sync(0xffffffffu, send2, step);
-            }
-        }
-        if (col0 + lane < n_out) {
-            atomicAdd(stats + col0 + lane, s1[0]);
-            atomicAdd(stats + n_out + col0 + lane, s2[0]);
-        }
-    }
+    if (stats != nullptr) conv_chunk_stats(v, row_ok, col0, n_out, stats, lane);
 }
 
 template <int kBlockN>
@@ -185,7 +212,7 @@ struct __align__(1024) ConvSmem {
 // stats (optional, fp32 [2][n_out]): per-output-channel sum and sum of squares of the STORED (bf16
 // rounded) outputs, accumulated with atomics -- the BatchNorm that follows needs no reduction pass.
 template <int kBlockN, bool kDgrad>
-__global__ void __launch_bounds__(kConvThreads, 1)
+__global__ void __launch_bounds__(kConvWideThreads, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                   const __grid_constant__ ConvGemmParams p, __nv_bfloat16* __restrict__ out,
                   const float* __restrict__ bias, float* __restrict__ stats) {
@@ -196,7 +223,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     using Smem = ConvSmem<kBlockN>;
     Smem& sm = *reinterpret_cast<Smem*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = uniform_warp_index(), lane = threadIdx.x & 31;
     const int cblocks = (p.a_channels + kGemmBlockK - 1) / kGemmBlockK;
     const int n_tiles = (p.n_out + kBlockN - 1) / kBlockN;
     const int p_tiles = p.tiles_w * p.tiles_h * p.tiles_n;
@@ -211,7 +238,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         }
         for (int a = 0; a < 2; ++a) {
             mbar_init(&sm.tmem_full[a], 1);
-            mbar_init(&sm.tmem_empty[a], 128);
+            mbar_init(&sm.tmem_empty[a], kConvWideThreads - 64);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -224,14 +251,14 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const uint32_t tmem_base = sm.tmem_base;
+    const uint32_t tmem_base = warp_uniform(sm.tmem_base);
     // Let the next kernel of the stream launch only now that this CTA owns its tensor memory: a dependent that
     // were resident earlier could take the columns this CTA is still waiting for and then wait for this grid.
     pdl_launch_dependents();
     pdl_wait();  // everything above is independent of the previous kernel's output
 
     if (warp == 0) {
-        if (lane == 0) {  // ---- TMA producer
+        if (elect_one()) {  // ---- TMA producer
             uint32_t it = 0;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
                 const int nt = tile % n_tiles;
@@ -265,7 +292,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {  // ---- MMA issuer
+        if (elect_one()) {  // ---- MMA issuer
             const uint32_t idesc = conv_instr_desc<kBlockN, false, kDgrad>();
             uint32_t it = 0, local_tile = 0;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local_tile) {
@@ -295,7 +322,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         }
     } else {
         // ---- epilogue
-        const int quarter = warp & 3;
+        const int quarter = warp & 3, cgroup = (warp - 2) >> 2;
         const int m_local = quarter * 32 + lane;
         const int lw = m_local % p.bw, lh = (m_local / p.bw) % p.bh, ln = m_local / (p.bw * p.bh);
         uint32_t local_tile = 0;
@@ -317,7 +344,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
                 (((long long)n * p.out_h + (h * p.os + p.class_oph[cls])) * p.out_w + (w * p.os + p.class_opw[cls])) *
                     (long long)p.out_pitch;
 #pragma unroll 1
-            for (int chunk = 0; chunk < kBlockN / 32; ++chunk) {
+            for (int chunk = cgroup; chunk < kBlockN / 32; chunk += 2) {
                 const int col0 = n0 + chunk * 32;
                 if (col0 >= p.n_out) break;
                 uint32_t r[32];
@@ -338,6 +365,226 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
+    }
+}
+
+// ---- 3 x 3, stride 1 with a shared-memory halo patch --------------------------------------------------------
+// The tap-by-tap kernel above brings the A tile in once PER TAP: 9 x 16 KB per 64 reduction channels, and the
+// ~46 B/clk an SM takes in from L2 is what bounds it on the wide feature maps (ResNet stages 1 / 2).  Here a CTA
+// owns an 8 (w) x 16 (h) patch of output pixels of one image and loads, per 64 reduction channels, ONE box of
+// 16 x 18 input pixels -- the tile plus its halo, 36 KB instead of 144 KB.  All nine taps read that box in place:
+// with the 128-byte swizzle one pixel is one 128-byte row, 8 rows (8 consecutive w) form a swizzle atom, and the
+// UMMA descriptor of tap (r, s) simply starts (r * 16 + s) rows further with the stride between 8-row groups
+// set to one patch line (2 048 B).  The start is then s rows off the 1 024-byte swizzle period; measured on
+// B200 the tensor core derives the swizzle phase from the absolute shared-memory address bits [7, 10), which
+// is exactly how TMA wrote the patch, so the base-offset field of the descriptor stays 0 (setting it to s, or
+// to 8 - s, gives wrong results).  Filters: nine 64 x 64 tiles per 64 reduction channels; when the layer has a
+// single such set (Cin, Cout <= 64) they are loaded once per CTA and stay resident.
+constexpr int kHaloW = 8, kHaloH = 16;              // output pixels of a tile
+constexpr int kHaloPatchW = 16, kHaloPatchH = 18;   // input pixels loaded for it
+constexpr int kHaloAStages = 3;
+constexpr uint32_t kHaloBytesA = kHaloPatchW * kHaloPatchH * 128;
+constexpr uint32_t kHaloBytesB = 64 * 64 * 2;
+
+struct HaloParams {
+    int n, h, w;
+    int k_channels;   // reduction channels
+    int n_out;        // output channels
+    int out_pitch;
+    int tiles_w, tiles_h;
+    int resident;     // one filter set for the whole launch
+};
+
+#ifdef DLS_CONV_TIMELINE
+// per-CTA clock64 stamps of the kernel's phases (development aid, tools/conv_timeline.py)
+__device__ long long g_conv_timeline[kNumSMs][16];
+#define DLS_TL(slot) (g_conv_timeline[blockIdx.x % kNumSMs][slot] = clock64())
+#else
+#define DLS_TL(slot) ((void)0)
+#endif
+
+struct __align__(1024) HaloSmem {
+    unsigned char a[kHaloAStages][kHaloBytesA];
+    unsigned char b[9][kHaloBytesB];
+    uint64_t a_full[kHaloAStages];
+    uint64_t a_empty[kHaloAStages];
+    uint64_t b_full[9];
+    uint64_t b_empty[9];
+    uint64_t tmem_full[2];
+    uint64_t tmem_empty[2];
+    uint32_t tmem_base;
+};
+
+__device__ __forceinline__ uint64_t umma_smem_desc_halo(uint32_t smem_addr) {
+    uint64_t desc = 0;
+    desc |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+    desc |= (uint64_t)1 << 16;
+    desc |= (uint64_t)((kHaloPatchW * 128) >> 4) << 32;  // next 8-pixel group = next patch line
+    desc |= (uint64_t)1 << 46;
+    desc |= (uint64_t)2 << 61;
+    return desc;
+}
+
+template <bool kDgrad>
+__global__ void __launch_bounds__(kConvWideThreads, 1)
+conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                 const __grid_constant__ HaloParams p, __nv_bfloat16* __restrict__ out,
+                 const float* __restrict__ bias, float* __restrict__ stats) {
+    extern __shared__ unsigned char smem_raw[];
+    constexpr int kBlockN = 64;
+    constexpr uint32_t kTmemCols = 2 * kBlockN;
+    HaloSmem& sm = *reinterpret_cast<HaloSmem*>(
+        (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    const int warp = uniform_warp_index(), lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) DLS_TL(0);
+    const int cblocks = (p.k_channels + 63) / 64;
+    const int n_tiles = (p.n_out + kBlockN - 1) / kBlockN;
+    const int p_tiles = p.tiles_w * p.tiles_h * p.n;
+    const int num_tiles = n_tiles * p_tiles;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+        for (int s = 0; s < kHaloAStages; ++s) {
+            mbar_init(&sm.a_full[s], 1);
+            mbar_init(&sm.a_empty[s], 1);
+        }
+        for (int s = 0; s < 9; ++s) {
+            mbar_init(&sm.b_full[s], 1);
+            mbar_init(&sm.b_empty[s], 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(&sm.tmem_full[a], 1);
+            mbar_init(&sm.tmem_empty[a], kConvWideThreads - 64);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm.tmem_base)),
+                     "r"(kTmemCols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = warp_uniform(sm.tmem_base);
+    pdl_launch_dependents();  // after the tensor-memory allocation, see conv_igemm_kernel
+    if (threadIdx.x == 0) DLS_TL(1);
+
+    if (warp == 0) {
+        if (elect_one()) {  // ---- TMA producer
+            pdl_wait();
+            DLS_TL(2);
+            if (p.resident) {
+                for (int t = 0; t < 9; ++t) {
+                    mbar_expect_tx(&sm.b_full[t], kHaloBytesB);
+                    if (!kDgrad) tma_load_3d(sm.b[t], &map_b, &sm.b_full[t], 0, t, 0);
+                    else tma_load_3d(sm.b[t], &map_b, &sm.b_full[t], 0, 8 - t, 0);
+                }
+            }
+            uint32_t ia = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const int nt = tile % n_tiles, pt = tile / n_tiles;
+                const int w0 = (pt % p.tiles_w) * kHaloW;
+                const int h0 = ((pt / p.tiles_w) % p.tiles_h) * kHaloH;
+                const int img = pt / (p.tiles_w * p.tiles_h);
+                for (int cb = 0; cb < cblocks; ++cb, ++ia) {
+                    const int s = ia % kHaloAStages;
+                    mbar_wait(&sm.a_empty[s], ((ia / kHaloAStages) & 1) ^ 1);
+                    mbar_expect_tx(&sm.a_full[s], kHaloBytesA);
+                    tma_load_5d(sm.a[s], &map_a, &sm.a_full[s], cb * 64, w0 - 1, 0, h0 - 1, img);
+                    if (!p.resident) {
+                        for (int t = 0; t < 9; ++t) {
+                            // slot t holds the filter tap that patch position t (row t / 3, column t % 3) meets
+                            mbar_wait(&sm.b_empty[t], (ia & 1) ^ 1);
+                            mbar_expect_tx(&sm.b_full[t], kHaloBytesB);
+                            if (!kDgrad) tma_load_3d(sm.b[t], &map_b, &sm.b_full[t], cb * 64, t, nt * kBlockN);
+                            else tma_load_3d(sm.b[t], &map_b, &sm.b_full[t], nt * kBlockN, 8 - t, cb * 64);
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (elect_one()) {  // ---- MMA issuer
+            const uint32_t idesc = conv_instr_desc<kBlockN, false, kDgrad>();
+            uint32_t ia = 0, local_tile = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local_tile) {
+                const uint32_t acc = local_tile & 1, use = local_tile >> 1;
+                mbar_wait(&sm.tmem_empty[acc], (use & 1) ^ 1);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t tmem_acc = tmem_base + acc * kBlockN;
+                for (int cb = 0; cb < cblocks; ++cb, ++ia) {
+                    const int s = ia % kHaloAStages;
+                    mbar_wait(&sm.a_full[s], (ia / kHaloAStages) & 1);
+                    if (ia == 0) DLS_TL(3);
+                    const uint32_t a_addr = smem_u32(sm.a[s]);
+#pragma unroll 1
+                    for (int t = 0; t < 9; ++t) {
+                        mbar_wait(&sm.b_full[t], p.resident ? 0u : (ia & 1));
+                        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                        const int pr = t / 3, pc = t - 3 * pr;
+                        const uint32_t a_tap = a_addr + (uint32_t)(pr * kHaloPatchW + pc) * 128;
+                        const uint32_t b_addr = smem_u32(sm.b[t]);
+#pragma unroll
+                        for (int kk = 0; kk < 4; ++kk) {
+                            const uint64_t da = umma_smem_desc_halo(a_tap + kk * 32);
+                            const uint64_t db = kDgrad ? umma_smem_desc_mn(b_addr + kk * 2048, 8192)
+                                                       : umma_smem_desc(b_addr + kk * 32);
+                            umma_bf16(tmem_acc, da, db, idesc, (cb | t | kk) != 0);
+                        }
+                        if (!p.resident) umma_commit(&sm.b_empty[t]);
+                    }
+                    umma_commit(&sm.a_empty[s]);
+                }
+                umma_commit(&sm.tmem_full[acc]);
+            }
+        }
+    } else {
+        // ---- epilogue
+        pdl_wait();
+        const int quarter = warp & 3, cgroup = (warp - 2) >> 2;
+        const int m_local = quarter * 32 + lane;
+        const int lw = m_local & (kHaloW - 1), lh = m_local / kHaloW;
+        uint32_t local_tile = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local_tile) {
+            const int nt = tile % n_tiles, pt = tile / n_tiles;
+            const int w = (pt % p.tiles_w) * kHaloW + lw;
+            const int h = ((pt / p.tiles_w) % p.tiles_h) * kHaloH + lh;
+            const int img = pt / (p.tiles_w * p.tiles_h);
+            const bool row_ok = w < p.w && h < p.h;
+            const int n0 = nt * kBlockN;
+            const uint32_t acc = local_tile & 1, use = local_tile >> 1;
+            mbar_wait(&sm.tmem_full[acc], use & 1);
+            if (threadIdx.x == 64 && local_tile < 4) DLS_TL(4 + 2 * local_tile);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t tmem_acc = tmem_base + acc * kBlockN;
+            __nv_bfloat16* dst_row = out + (((long long)img * p.h + h) * p.w + w) * (long long)p.out_pitch;
+#pragma unroll 1
+            for (int chunk = cgroup; chunk < kBlockN / 32; chunk += 2) {
+                const int col0 = n0 + chunk * 32;
+                if (col0 >= p.n_out) break;
+                uint32_t r[32];
+                tmem_ld_32x32(tmem_acc + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(chunk * 32), r);
+                if (threadIdx.x == 64 && local_tile == 0 && chunk == 0) DLS_TL(12);
+                float v[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+                conv_store_chunk(v, row_ok, dst_row, col0, p.n_out, bias, stats, lane);
+                if (threadIdx.x == 64 && local_tile == 0 && chunk == 0) DLS_TL(13);
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            mbar_arrive(&sm.tmem_empty[acc]);
+            if (threadIdx.x == 64 && local_tile < 4) DLS_TL(5 + 2 * local_tile);
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (threadIdx.x == 0) DLS_TL(14);
     if (warp == 1) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
@@ -391,7 +638,7 @@ conv_igemm_splitk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
     constexpr int kStages = Smem::kStages;
     Smem& sm = *reinterpret_cast<Smem*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = uniform_warp_index(), lane = threadIdx.x & 31;
     const int crank = (int)cluster_rank();
     const int cblocks = (p.a_channels + kGemmBlockK - 1) / kGemmBlockK;
     const int n_tiles = (p.n_out + kBlockN - 1) / kBlockN;
@@ -426,7 +673,7 @@ conv_igemm_splitk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
     asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const uint32_t tmem_base = sm.tmem_base;
+    const uint32_t tmem_base = warp_uniform(sm.tmem_base);
     // Let the next kernel of the stream launch only now that this CTA owns its tensor memory: a dependent that
     // were resident earlier could take the columns this CTA is still waiting for and then wait for this grid.
     pdl_launch_dependents();
@@ -436,7 +683,7 @@ conv_igemm_splitk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
     const int n0 = (pt / (p.tiles_w * p.tiles_h)) * p.bn;
 
     if (warp == 0) {
-        if (lane == 0) {  // ---- TMA producer over this CTA's share of the K blocks
+        if (elect_one()) {  // ---- TMA producer over this CTA's share of the K blocks
             const int tap0 = p.class_tap0[cls];
             uint32_t it = 0;
             for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
@@ -459,7 +706,7 @@ conv_igemm_splitk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {  // ---- MMA issuer
+        if (elect_one()) {  // ---- MMA issuer
             const uint32_t idesc = conv_instr_desc<kBlockN, false, kDgrad>();
             uint32_t it = 0;
             for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
@@ -604,7 +851,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_const
     using Smem = WgradSmem<kBlockN, kStages>;
     Smem& sm = *reinterpret_cast<Smem*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = uniform_warp_index(), lane = threadIdx.x & 31;
     const int m_tiles = (p.c_out + 127) / 128;
     const int n_tiles = (p.c_in + kBlockN - 1) / kBlockN;
     const int p_tiles = p.tiles_w * p.tiles_h * p.tiles_n;
@@ -632,7 +879,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_const
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const uint32_t tmem_base = sm.tmem_base;
+    const uint32_t tmem_base = warp_uniform(sm.tmem_base);
     // Let the next kernel of the stream launch only now that this CTA owns its tensor memory: a dependent that
     // were resident earlier could take the columns this CTA is still waiting for and then wait for this grid.
     pdl_launch_dependents();
@@ -649,7 +896,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_const
     };
 
     if (warp == 0) {
-        if (lane == 0) {
+        if (elect_one()) {  // ---- TMA producer
             uint32_t it = 0;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
                 int nt, mt, ti, sp;
@@ -678,7 +925,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_const
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        if (elect_one()) {  // ---- MMA issuer
             const uint32_t idesc = conv_instr_desc<kBlockN, true, true>();
             uint32_t it = 0, local_tile = 0;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local_tile) {
@@ -899,6 +1146,40 @@ static int pick_block_n(int n_out, long long p_tiles) {
     return (p_tiles * ((n_out + 127) / 128) >= 100) ? 128 : 64;
 }
 
+// 3 x 3 / stride 1 / pad 1 layers wide enough for 8 x 16 pixel tiles take the halo-patch kernel
+static bool halo_eligible(const DlsConvShape& cs) {
+    static const int enabled = [] { const char* e = getenv("DLS_CONV_HALO"); return e ? atoi(e) : 1; }();
+    return enabled && cs.r == 3 && cs.s == 3 && cs.stride == 1 && cs.pad_h == 1 && cs.pad_w == 1 && cs.w % kHaloW == 0 &&
+           cs.w >= kHaloPatchW && cs.h >= kHaloH;
+}
+
+template <bool kDgrad>
+static int launch_halo(const void* a, const void* w, void* out, const float* bias, float* stats, const DlsConvShape& cs,
+                       cudaStream_t st) {
+    HaloParams p = {};
+    p.n = cs.n; p.h = cs.h; p.w = cs.w;
+    p.k_channels = kDgrad ? cs.c_out : cs.c_in;
+    p.n_out = kDgrad ? cs.c_in : cs.c_out;
+    const int a_pitch = kDgrad ? (cs.y_pitch ? cs.y_pitch : cs.c_out) : (cs.x_pitch ? cs.x_pitch : cs.c_in);
+    p.out_pitch = kDgrad ? (cs.x_pitch ? cs.x_pitch : cs.c_in) : (cs.y_pitch ? cs.y_pitch : cs.c_out);
+    p.tiles_w = cs.w / kHaloW; p.tiles_h = (cs.h + kHaloH - 1) / kHaloH;
+    p.resident = (p.k_channels <= 64 && p.n_out <= 64) ? 1 : 0;
+    CUtensorMap map_a, map_b;
+    if (int rc = make_act_map(&map_a, a, cs.n, cs.h, cs.w, p.k_channels, a_pitch, 1, kHaloPatchW, kHaloPatchH, 1)) return rc;
+    if (int rc = make_filter_map(&map_b, w, cs.c_out, 9, cs.c_in, 64)) return rc;
+    const long long tiles = (long long)p.tiles_w * p.tiles_h * cs.n * ((p.n_out + 63) / 64);
+    auto kernel = conv_halo_kernel<kDgrad>;
+    const size_t smem = sizeof(HaloSmem) + 1024;
+    static thread_local bool configured = false;
+    if (!configured) {
+        if (int rc = set_smem(kernel, smem)) return rc;
+        configured = true;
+    }
+    DLS_CHECK(launch_pdl(kernel, dim3((unsigned)(tiles < kNumSMs ? tiles : kNumSMs)), dim3(kConvWideThreads), smem, st, 0,
+                         map_a, map_b, p, (__nv_bfloat16*)out, bias, stats));
+    return 0;
+}
+
 }  // namespace dls
 
 using namespace dls;
@@ -915,6 +1196,19 @@ extern "C" int dls_tensor_map_probe(int rank, const unsigned long long* dims, co
                        (const cuuint32_t*)elem_strides, CU_TENSOR_MAP_INTERLEAVE_NONE, (CUtensorMapSwizzle)swizzle,
                        CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
 }
+
+#ifdef DLS_CONV_TIMELINE
+extern "C" int dls_conv_timeline(long long* host_out, int reset) {
+    if (reset) {
+        static long long zeros[kNumSMs][16];
+        DLS_CHECK(cudaMemcpyToSymbol(g_conv_timeline, zeros, sizeof(zeros)));
+        return 0;
+    }
+    DLS_CHECK(cudaDeviceSynchronize());
+    DLS_CHECK(cudaMemcpyFromSymbol(host_out, g_conv_timeline, sizeof(long long) * kNumSMs * 16));
+    return 0;
+}
+#endif
 
 extern "C" int dls_conv_supported(const DlsConvShape* cs) { return check_conv(*cs, "probe") == 0 ? 1 : 0; }
 
@@ -940,6 +1234,11 @@ extern "C" int dls_conv_fprop(const void* x, const void* w, void* y, const float
             t.dw = (int16_t)floor_div(qw, cs.stride); t.pw = (uint8_t)(qw - t.dw * cs.stride);
             t.widx = (uint16_t)(r * cs.s + s);
         }
+    if (halo_eligible(cs)) {
+        if (int rc = launch_halo<false>(x, w, y, bias, stats, cs, (cudaStream_t)stream)) return rc;
+        DLS_LAUNCHED("conv_halo_kernel<fprop>");
+        return 0;
+    }
     const long long p_tiles = (long long)p.tiles_w * p.tiles_h * p.tiles_n;
     const int cblocks = (cs.c_in + 63) / 64;
     if (const int split = pick_split(cs.c_out, p_tiles * ((cs.c_out + 127) / 128), cs.r * cs.s * cblocks)) {
@@ -968,7 +1267,7 @@ extern "C" int dls_conv_fprop(const void* x, const void* w, void* y, const float
             if (int rc = set_smem(conv_igemm_kernel<BN, false>, smem)) return rc;                             \
             configured = true;                                                                                \
         }                                                                                                     \
-        DLS_CHECK(launch_pdl(conv_igemm_kernel<BN, false>, grid, dim3(kConvThreads), smem, st, 0, map_a, map_b, p, \
+        DLS_CHECK(launch_pdl(conv_igemm_kernel<BN, false>, grid, dim3(kConvWideThreads), smem, st, 0, map_a, map_b, p, \
                              (__nv_bfloat16*)y, bias, stats));                                                \
     } while (0)
     if (block_n == 128) DLS_CONV_LAUNCH(128);
@@ -985,6 +1284,11 @@ extern "C" int dls_conv_dgrad(const void* dy, const void* w, void* dx, const Dls
     const int oh = (cs.h + 2 * cs.pad_h - cs.r) / cs.stride + 1, ow = (cs.w + 2 * cs.pad_w - cs.s) / cs.stride + 1;
     const int st_ = cs.stride;
     if (st_ == 2 && (oh != cs.h / 2 || ow != cs.w / 2)) return fail_msg("dls_conv_dgrad: stride 2 needs OH == H/2, OW == W/2");
+    if (halo_eligible(cs)) {
+        if (int rc = launch_halo<true>(dy, w, dx, nullptr, nullptr, cs, (cudaStream_t)stream)) return rc;
+        DLS_LAUNCHED("conv_halo_kernel<dgrad>");
+        return 0;
+    }
     ConvGemmParams p = {};
     p.pn = cs.n; p.ph = cs.h / st_; p.pw = cs.w / st_;
     choose_box(p.pw, p.ph, cs.n, p.bw, p.bh, p.bn);
@@ -1037,7 +1341,7 @@ extern "C" int dls_conv_dgrad(const void* dy, const void* w, void* dx, const Dls
             if (int rc = set_smem(conv_igemm_kernel<BN, true>, smem)) return rc;                              \
             configured = true;                                                                                \
         }                                                                                                     \
-        DLS_CHECK(launch_pdl(conv_igemm_kernel<BN, true>, grid, dim3(kConvThreads), smem, st, 0, map_a, map_b, p, \
+        DLS_CHECK(launch_pdl(conv_igemm_kernel<BN, true>, grid, dim3(kConvWideThreads), smem, st, 0, map_a, map_b, p, \
                              (__nv_bfloat16*)dx, (const float*)nullptr, (float*)nullptr));                    \
     } while (0)
     if (block_n == 128) DLS_CONV_LAUNCH(128);

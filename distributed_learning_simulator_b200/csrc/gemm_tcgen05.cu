@@ -48,7 +48,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
     using Smem = GemmSmem<kBlockN>;
     Smem& sm = *reinterpret_cast<Smem*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = uniform_warp_index(), lane = threadIdx.x & 31;
     const int num_kb = (k + kGemmBlockK - 1) / kGemmBlockK;
     const int m_tiles = (m + kGemmBlockM - 1) / kGemmBlockM;
     const int n_tiles = (n + kBlockN - 1) / kBlockN;
@@ -76,10 +76,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const uint32_t tmem_base = sm.tmem_base;
+    const uint32_t tmem_base = warp_uniform(sm.tmem_base);
 
     if (warp == 0) {
-        if (lane == 0) {  // ---- TMA producer: the ring runs straight through tile boundaries
+        if (elect_one()) {  // ---- TMA producer: the ring runs straight through tile boundaries
             uint32_t it = 0;
             for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
                 const int mt = (int)(tile % m_tiles), nt = (int)((tile / m_tiles) % n_tiles);
@@ -95,7 +95,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {  // ---- MMA issuer
+        if (elect_one()) {  // ---- MMA issuer
             const uint32_t idesc = umma_instr_desc<kBlockN>();
             uint32_t it = 0, local_tile = 0;
             for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local_tile) {
@@ -270,9 +270,9 @@ gemm_bf16_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap map_a, const _
     using Smem = PairSmem<kBlockN>;
     Smem& sm = *reinterpret_cast<Smem*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = uniform_warp_index(), lane = threadIdx.x & 31;
     uint32_t rank;
-    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+    rank = blockIdx.x & 1;  // == %cluster_ctarank for the (2, 1, 1) cluster, and provably warp-uniform
     const bool leader = rank == 0;
     const int num_kb = (k + kGemmBlockK - 1) / kGemmBlockK;
     const int m_tiles = (m + kPairM - 1) / kPairM;
@@ -304,10 +304,10 @@ gemm_bf16_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap map_a, const _
     asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const uint32_t tmem_base = sm.tmem_base;
+    const uint32_t tmem_base = warp_uniform(sm.tmem_base);
 
     if (warp == 0) {
-        if (lane == 0) {  // ---- TMA producer, both CTAs: my half of A and my half of B
+        if (elect_one()) {  // ---- TMA producer, both CTAs: my half of A and my half of B
             uint32_t it = 0;
             for (long long tile = first_tile; tile < num_tiles; tile += tile_step) {
                 const int mt = (int)(tile % m_tiles), nt = (int)((tile / m_tiles) % n_tiles);
@@ -325,7 +325,9 @@ gemm_bf16_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap map_a, const _
             }
         }
     } else if (warp == 1) {
-        if (lane == 0 && leader) {  // ---- MMA issuer: the leader CTA only
+        if (!leader) {
+            // the peer CTA's tensor core is driven by the leader's cta_group::2 instructions
+        } else if (elect_one()) {  // ---- MMA issuer: the leader CTA only
             // instruction descriptor as in the single-CTA kernel but M = 256
             uint32_t idesc = 0;
             idesc |= 1u << 4;

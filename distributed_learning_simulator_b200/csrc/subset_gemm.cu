@@ -256,7 +256,7 @@ subset_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, int a_shar
     using Smem = SubsetSmem<kBlockN>;
     Smem& sm = *reinterpret_cast<Smem*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = uniform_warp_index(), lane = threadIdx.x & 31;
     const int num_kb = (k_a + kGemmBlockK - 1) / kGemmBlockK;
     const int m_tiles = (m + kGemmBlockM - 1) / kGemmBlockM;
     const int n_tiles = (n_total + kBlockN - 1) / kBlockN;
@@ -292,10 +292,10 @@ subset_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, int a_shar
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     if (kCluster > 1) cluster_sync_all();  // the peer's barriers are initialised before anyone signals them
-    const uint32_t tmem_base = sm.tmem_base;
+    const uint32_t tmem_base = warp_uniform(sm.tmem_base);
 
     if (warp == 0) {
-        if (lane == 0) {  // ---- TMA producer (activations only)
+        if (elect_one()) {  // ---- TMA producer (activations only)
             uint32_t it = 0;
             for (long long tile = first_tile; tile < num_tiles; tile += tile_step) {
                 const int mt = (int)(tile % m_groups) * kCluster + (int)rank;
@@ -311,7 +311,7 @@ subset_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, int a_shar
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {  // ---- MMA issuer
+        if (elect_one()) {  // ---- MMA issuer
             const uint32_t idesc = umma_instr_desc<kBlockN>();
             uint32_t it = 0, local_tile = 0;
             for (long long tile = first_tile; tile < num_tiles; tile += tile_step, ++local_tile) {
@@ -429,7 +429,7 @@ subset_gemm_stationary_kernel(const __grid_constant__ CUtensorMap map_a, int a_s
     using Smem = StationarySmem<kBlockN>;
     Smem& sm = *reinterpret_cast<Smem*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = uniform_warp_index(), lane = threadIdx.x & 31;
     const int num_kb = (k_a + kGemmBlockK - 1) / kGemmBlockK;  // <= kStationaryMaxKb (host checks)
     const int m_tiles = (m + kGemmBlockM - 1) / kGemmBlockM;
     const int n_tiles = (n_total + kBlockN - 1) / kBlockN;
@@ -465,7 +465,7 @@ subset_gemm_stationary_kernel(const __grid_constant__ CUtensorMap map_a, int a_s
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     if (kCluster > 1) cluster_sync_all();
-    const uint32_t tmem_base = sm.tmem_base;
+    const uint32_t tmem_base = warp_uniform(sm.tmem_base);
 
     // unit -> (first M group, number of M groups, N tile, coalition)
 #define DLS_UNIT_DECODE(unit)                                                          \
@@ -476,7 +476,7 @@ subset_gemm_stationary_kernel(const __grid_constant__ CUtensorMap map_a, int a_s
     const int mg1 = mg0 + m_run < m_groups ? mg0 + m_run : m_groups;
 
     if (warp == 0) {
-        if (lane == 0) {  // ---- TMA producer (activations)
+        if (elect_one()) {  // ---- TMA producer (activations)
             uint32_t it = 0;
             for (long long unit = first_unit; unit < num_units; unit += unit_step) {
                 DLS_UNIT_DECODE(unit)
@@ -495,7 +495,7 @@ subset_gemm_stationary_kernel(const __grid_constant__ CUtensorMap map_a, int a_s
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {  // ---- MMA issuer
+        if (elect_one()) {  // ---- MMA issuer
             const uint32_t idesc = umma_instr_desc<kBlockN>();
             uint32_t it = 0, local_tile = 0, local_unit = 0;
             for (long long unit = first_unit; unit < num_units; unit += unit_step, ++local_unit) {

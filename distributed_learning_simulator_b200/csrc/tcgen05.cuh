@@ -18,6 +18,20 @@ constexpr uint32_t kBytesA = kGemmBlockM * kGemmBlockK * 2;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+// Single-thread roles (TMA producer, MMA issuer).  tcgen05.mma / cp.async.bulk.tensor take their operands from
+// uniform registers.  Under `if (lane == 0)` the compiler cannot prove the operands warp-uniform and wraps EVERY
+// such instruction in a per-lane loop (ELECT ... BRA.U.ANY) that waits on the instruction's scoreboard: measured on
+// B200 (tools/umma_rate.cu) that costs 143 clk per UMMA whatever its N, against 48 / 64 / 126 clk for N = 64 /
+// 128 / 256 when the UMMAs are issued back to back.  So: the warp index and everything read from shared memory
+// are broadcast from lane 0 (warp-uniform by construction) and the role's thread is picked with elect.sync.
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+__device__ __forceinline__ int uniform_warp_index() { return __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); }
+__device__ __forceinline__ uint32_t warp_uniform(uint32_t v) { return __shfl_sync(0xffffffffu, v, 0); }
+
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
 }

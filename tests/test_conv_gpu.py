@@ -16,7 +16,9 @@ RESNET18 = [
     (64, 512, 4, 4, 512, 3, 1, 1),
 ]
 ODD = [(10, 24, 12, 12, 40, 3, 1, 1), (3, 72, 7, 9, 16, 1, 1, 0), (5, 64, 10, 6, 72, 3, 2, 1), (37, 8, 28, 28, 8, 5, 1, 2),
-       (1250, 64, 32, 32, 64, 3, 1, 1)]
+       (1250, 64, 32, 32, 64, 3, 1, 1),
+       # halo-patch kernel: partial tile in h, channel tails on both sides, several filter sets
+       (3, 40, 24, 16, 72, 3, 1, 1), (2, 136, 16, 24, 64, 3, 1, 1), (5, 64, 40, 32, 64, 3, 1, 1)]
 
 
 def _case(n, ci, h, w, co, k, st, pad, seed=0):

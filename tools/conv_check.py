@@ -29,6 +29,8 @@ SHAPES = [
     (10, 24, 12, 12, 40, 3, 1, 1),     # odd sizes: partial boxes, channel tails
     (3, 72, 7, 9, 16, 1, 1, 0),
     (5, 64, 10, 6, 72, 3, 2, 1),
+    (3, 40, 24, 16, 72, 3, 1, 1),      # halo-patch kernel with tails
+    (2, 136, 16, 24, 64, 3, 1, 1),
 ]
 
 
