@@ -113,7 +113,7 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32])
 // column sums over the warp's 32 rows: butterfly that halves the value count per step, lane l ends with the
 // totals of column l
 __device__ __forceinline__ void conv_chunk_stats(const float (&v)[32], bool row_ok, int col0, int n_out,
-                                                 float* __restrict__ stats, int lane) {
+                                                 float* sum_dst, float* sq_dst, int lane) {
     float s1[32], s2[32];
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
@@ -136,8 +136,8 @@ __device__ __forceinline__ void conv_chunk_stats(const float (&v)[32], bool row_
         }
     }
     if (col0 + lane < n_out) {
-        atomicAdd(stats + col0 + lane, s1[0]);
-        atomicAdd(stats + n_out + col0 + lane, s2[0]);
+        atomicAdd(sum_dst + col0 + lane, s1[0]);
+        atomicAdd(sq_dst + col0 + lane, s2[0]);
     }
 }
 
@@ -145,7 +145,7 @@ __device__ __forceinline__ void conv_chunk_stats(const float (&v)[32], bool row_
 // the stored bf16, 128-bit stores, and -- when `stats` is given -- per-channel sum / sum of squares over the
 // warp's 32 rows added to stats[0][c], stats[1][c] (the BatchNorm that follows needs no reduction pass).
 __device__ __forceinline__ void conv_store_chunk(float (&v)[32], bool row_ok, __nv_bfloat16* dst_row, int col0,
-                                                 int n_out, const float* __restrict__ bias, float* __restrict__ stats,
+                                                 int n_out, const float* __restrict__ bias, float* sum_dst, float* sq_dst,
                                                  int lane) {
     __nv_bfloat16* dst = dst_row + col0;
     if (col0 + 32 <= n_out && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
@@ -169,14 +169,14 @@ __device__ __forceinline__ void conv_store_chunk(float (&v)[32], bool row_ok, __
                 reinterpret_cast<uint4*>(dst)[q] =
                     make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
         }
-        if (stats != nullptr) {
+        if (sum_dst != nullptr) {
             // statistics and consumers see the value that is stored: widen the packed bf16 back (a shift / a mask)
 #pragma unroll
             for (int e = 0; e < 16; ++e) {
                 v[2 * e] = __uint_as_float(packed[e] << 16);
                 v[2 * e + 1] = __uint_as_float(packed[e] & 0xffff0000u);
             }
-            conv_chunk_stats(v, row_ok, col0, n_out, stats, lane);
+            conv_chunk_stats(v, row_ok, col0, n_out, sum_dst, sq_dst, lane);
         }
         return;
     }
@@ -190,7 +190,31 @@ __device__ __forceinline__ void conv_store_chunk(float (&v)[32], bool row_ok, __
         for (int j = 0; j < 32; ++j)
             if (col0 + j < n_out) dst[j] = __float2bfloat16(v[j]);
     }
-    if (stats != nullptr) conv_chunk_stats(v, row_ok, col0, n_out, stats, lane);
+    if (sum_dst != nullptr) conv_chunk_stats(v, row_ok, col0, n_out, sum_dst, sq_dst, lane);
+}
+
+// A persistent CTA adds the column sums of all its tiles into shared memory and flushes them once: with one global
+// atomic per warp, chunk and tile the ResNet stage-1 layer sent 2 048 atomics to each of its 128 addresses, 4 us
+// of L2 serialisation.
+constexpr int kConvStatChannels = 512;
+struct ConvStatAcc {
+    float sum[kConvStatChannels];
+    float sq[kConvStatChannels];
+};
+__device__ __forceinline__ void conv_stat_acc_zero(ConvStatAcc& acc) {
+    for (int i = threadIdx.x; i < kConvStatChannels; i += blockDim.x) {
+        acc.sum[i] = 0.f;
+        acc.sq[i] = 0.f;
+    }
+}
+__device__ __forceinline__ void conv_stat_acc_flush(const ConvStatAcc& acc, float* __restrict__ stats, int n_out) {
+    for (int i = threadIdx.x; i < n_out; i += blockDim.x) {
+        const float a = acc.sum[i], b = acc.sq[i];
+        if (b != 0.f) {  // a channel this CTA never produced, or one that is all zero, adds nothing
+            atomicAdd(stats + i, a);
+            atomicAdd(stats + n_out + i, b);
+        }
+    }
 }
 
 template <int kBlockN>
@@ -206,6 +230,7 @@ struct __align__(1024) ConvSmem {
     uint64_t tmem_full[2];
     uint64_t tmem_empty[2];
     uint32_t tmem_base;
+    ConvStatAcc stat;
 };
 
 // ---- fprop / dgrad ------------------------------------------------------------------------------
@@ -242,6 +267,10 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    const bool stat_local = stats != nullptr && p.n_out <= kConvStatChannels;
+    if (stat_local) conv_stat_acc_zero(sm.stat);
+    float* const stat_sum = stats == nullptr ? nullptr : (stat_local ? sm.stat.sum : stats);
+    float* const stat_sq = stats == nullptr ? nullptr : (stat_local ? sm.stat.sq : stats + p.n_out);
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm.tmem_base)),
                      "r"(kTmemCols)
@@ -357,7 +386,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
                 float v[32];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-                conv_store_chunk(v, row_ok, dst_row, col0, p.n_out, bias, stats, lane);
+                conv_store_chunk(v, row_ok, dst_row, col0, p.n_out, bias, stat_sum, stat_sq, lane);
             }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             mbar_arrive(&sm.tmem_empty[acc]);
@@ -365,6 +394,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
+    if (stat_local) conv_stat_acc_flush(sm.stat, stats, p.n_out);
     if (warp == 1) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
@@ -416,6 +446,7 @@ struct __align__(1024) HaloSmem {
     uint64_t tmem_full[2];
     uint64_t tmem_empty[2];
     uint32_t tmem_base;
+    ConvStatAcc stat;
 };
 
 __device__ __forceinline__ uint64_t umma_smem_desc_halo(uint32_t smem_addr) {
@@ -462,6 +493,10 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    const bool stat_local = stats != nullptr && p.n_out <= kConvStatChannels;
+    if (stat_local) conv_stat_acc_zero(sm.stat);
+    float* const stat_sum = stats == nullptr ? nullptr : (stat_local ? sm.stat.sum : stats);
+    float* const stat_sq = stats == nullptr ? nullptr : (stat_local ? sm.stat.sq : stats + p.n_out);
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm.tmem_base)),
                      "r"(kTmemCols)
@@ -574,7 +609,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                 float v[32];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-                conv_store_chunk(v, row_ok, dst_row, col0, p.n_out, bias, stats, lane);
+                conv_store_chunk(v, row_ok, dst_row, col0, p.n_out, bias, stat_sum, stat_sq, lane);
                 if (threadIdx.x == 64 && local_tile == 0 && chunk == 0) DLS_TL(13);
             }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -585,6 +620,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (threadIdx.x == 0) DLS_TL(14);
+    if (stat_local) conv_stat_acc_flush(sm.stat, stats, p.n_out);
     if (warp == 1) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
@@ -800,7 +836,7 @@ conv_igemm_splitk_kernel(const __grid_constant__ CUtensorMap map_a, const __grid
             for (int src = 0; src < kSplit - 1; ++src)
 #pragma unroll
                 for (int j = 0; j < 32; ++j) v[j] += sm.recv[src][chunk * 32 + j][m_local];
-            conv_store_chunk(v, row_ok, dst_row, col0, p.n_out, bias, stats, lane);
+            conv_store_chunk(v, row_ok, dst_row, col0, p.n_out, bias, stats, stats ? stats + p.n_out : nullptr, lane);
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
