@@ -205,7 +205,9 @@ def run_ours(args) -> dict:
         counters0 = (runtime.launch_count(), graph_step.CAPTURE_LAUNCHES[0], graph_step.OWN_REPLAYED_KERNELS[0])
         conf = config_dict(args.config, args.gpus, rounds, args.dtype, storage)
         try:
-            train(load_config_from_dict(conf))
+            config = load_config_from_dict(conf)
+            config.apply_global_config()  # log level (100 workers at INFO write tens of MB of log) and the seed
+            train(config)
         finally:
             remove_round_observer(timer)
         # every round launches the same kernels, so the timed rounds' share of the run's exact totals

@@ -10,6 +10,27 @@ from ..engine.model_util import ModelUtil
 from .context import get_context, is_distributed  # noqa: F401
 
 
+def _wait_or_abort(task: Any, rank: int, grace_seconds: float = 20.0) -> None:
+    """Waits for the local roles.  When one of them has died, its local peers are woken by the topology, but roles
+    of OTHER ranks (and local ones already inside a collective) would wait for ever: after a grace period the
+    process exits non-zero, which makes the launcher (torch.distributed.run) take the whole job down."""
+    import logging
+    import os
+    import time
+
+    deadline = None
+    while not task.wait(timeout=1.0):
+        if not task.errors:
+            continue
+        if deadline is None:
+            deadline = time.monotonic() + grace_seconds
+        elif time.monotonic() > deadline:
+            get_logger().error("rank %s: %s role(s) failed and the others are still blocked after %.0f s; "
+                               "aborting the job: %r", rank, len(task.errors), grace_seconds, task.errors[0])
+            logging.shutdown()
+            os._exit(1)
+
+
 def train_distributed(config: Any, practitioners: None | set, task_id: int | None) -> None:
     from ..algorithm_factory import get_worker_config
     from ..training import _Task, _last_results, _write_trace
@@ -32,7 +53,7 @@ def train_distributed(config: Any, practitioners: None | set, task_id: int | Non
     task = _Task(task_id, config, worker_config)
     threading.current_thread().name = f"rank {ctx.rank}"
     task.start()
-    task.wait()
+    _wait_or_abort(task, ctx.rank)
     task.raise_errors()
     if ctx.rank == 0:
         _write_trace(config)

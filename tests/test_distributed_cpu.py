@@ -110,3 +110,36 @@ def test_methods_under_two_ranks(tmp_path):
     r0, r1 = (json.load(open(tmp_path / f"multi_{r}.json")) for r in range(2))
     assert r0 == r1 and set(r0) == set(_METHODS)
     assert all(len(perf) >= 1 for perf in r0.values())
+
+
+FAULT_SCRIPT = r"""
+import os, sys
+sys.path.insert(0, {root!r})
+from distributed_learning_simulator_b200 import load_config_from_dict, train
+from distributed_learning_simulator_b200.worker.aggregation_worker import AggregationWorker
+original = AggregationWorker._get_sent_data
+def broken(self):
+    if self.worker_id == 1 and self._round_num == 1:
+        raise ValueError("injected fault in worker 1")
+    return original(self)
+AggregationWorker._get_sent_data = broken
+train(load_config_from_dict({conf!r}))
+"""
+
+
+def test_a_dead_worker_takes_the_whole_job_down(tmp_path):
+    """A role that raises on one rank must not leave the other rank waiting in a collective for ever: the failing
+    rank exits non-zero after a grace period and the launcher tears the job down (parallel/launch.py)."""
+    import time
+
+    conf = {**_TINY, "distributed_algorithm": "fed_avg", "round": 2}
+    script = tmp_path / "fault.py"
+    script.write_text(FAULT_SCRIPT.format(root=ROOT, conf=conf))
+    env = dict(os.environ, DLS_FORCE_CPU="1", DLS_OUTPUT_ROOT=str(tmp_path), OMP_NUM_THREADS="2")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), str(script)]
+    start = time.monotonic()
+    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=240)
+    assert res.returncode != 0
+    assert time.monotonic() - start < 200
+    assert "injected fault" in res.stderr + res.stdout
