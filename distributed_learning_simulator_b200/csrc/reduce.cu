@@ -58,6 +58,10 @@ __device__ __forceinline__ void multimem_st_f1(float* mc, float v) {
 
 constexpr int kReduceThreads = 256;
 constexpr int kMaxDsts = 8;
+// "last block out" counters of the cross-GPU reduce, one slot per launch in flight (module globals exist once per
+// device, need no allocation and are therefore safe under stream capture)
+constexpr int kDoneSlots = 64;
+__device__ unsigned int g_done_counters[kDoneSlots];
 
 struct DstTable { float* p[kMaxDsts]; };
 
@@ -66,7 +70,7 @@ __global__ void __launch_bounds__(kReduceThreads, 2)
 fedavg_reduce_f32_kernel(const float* const* __restrict__ rows, const float* __restrict__ weights, int n_rows,
                          const float* __restrict__ old, float old_scale, double inv_total, DstTable dsts,
                          int n_dsts, float* __restrict__ mc_dst, long long lo, long long hi, uint32_t* const* peer_flags, int n_ranks, int rank,
-                         uint32_t epoch, uint32_t* __restrict__ nan_flag, unsigned int* done_counter) {
+                         uint32_t epoch, uint32_t* __restrict__ nan_flag, int done_slot) {
     extern __shared__ unsigned char smem_raw[];
     const float** s_rows = reinterpret_cast<const float**>(smem_raw);
     float* s_w = reinterpret_cast<float*>(s_rows + n_rows);
@@ -165,7 +169,9 @@ fedavg_reduce_f32_kernel(const float* const* __restrict__ rows, const float* __r
     // scalar tail (at most 3 elements, only in the slice that ends at P)
     for (long long i = lo + (n_vec << 2) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
         double a = 0.0;
-        for (int k = 0; k < n_rows; ++k) a += (double)s_w[k] * s_rows[k][i];
+        // peer rows were written by other GPUs: read them past the (non-coherent) L1 like the vector path does
+        for (int k = 0; k < n_rows; ++k)
+            a += (double)s_w[k] * (kPeer ? *reinterpret_cast<const volatile float*>(s_rows[k] + i) : s_rows[k][i]);
         float r = (float)((double)old_scale * (old ? old[i] : 0.f) + a * inv_total);
         saw_nan |= (r != r);
         if (kPeer && mc_dst != nullptr) multimem_st_f1(mc_dst + i, r);
@@ -180,6 +186,7 @@ fedavg_reduce_f32_kernel(const float* const* __restrict__ rows, const float* __r
         __shared__ bool is_last;
         __threadfence_system();
         __syncthreads();
+        unsigned int* done_counter = &g_done_counters[done_slot];
         if (threadIdx.x == 0) is_last = (atomicAdd(done_counter, 1u) == gridDim.x - 1);
         __syncthreads();
         if (is_last && threadIdx.x == 0) {
@@ -307,7 +314,6 @@ extern "C" const char* dls_last_error(void) { return g_last_error; }
 extern "C" long long dls_launch_count(void) { return g_launch_count.load(); }
 extern "C" void dls_reset_launch_count(void) { g_launch_count.store(0); }
 
-static unsigned int* g_done_counter[16] = {nullptr};
 
 static int fedavg_reduce_f32_impl(const float* const* rows, const float* weights, int n_rows, const float* old,
                                   float old_scale, double inv_total, float* const* dsts, int n_dsts, float* mc_dst,
@@ -323,13 +329,10 @@ static int fedavg_reduce_f32_impl(const float* const* rows, const float* weights
     const long long n_vec = ((hi - lo) >> 2) + 1;
     const bool peer = peer_flags != nullptr && n_ranks > 1;
     if (peer) {
-        int dev = 0;
-        DLS_CHECK(cudaGetDevice(&dev));
-        if (dev < 0 || dev >= 16) return fail_msg("dls_fedavg_reduce_f32: device index out of range");
-        if (g_done_counter[dev] == nullptr) {
-            DLS_CHECK(cudaMalloc(&g_done_counter[dev], sizeof(unsigned int)));
-            DLS_CHECK(cudaMemset(g_done_counter[dev], 0, sizeof(unsigned int)));
-        }
+        // last-block counter of this launch: a slot of the per-device pool, so reductions that overlap on one GPU
+        // (two tasks, two streams) never share one; the kernel leaves its slot at zero
+        static std::atomic<unsigned int> next_slot{0};
+        const int done_slot = (int)(next_slot.fetch_add(1) % kDoneSlots);
         // every block must be co-resident: it spins on the peers' flags
         int per_sm = 0;
         DLS_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fedavg_reduce_f32_kernel<true>,
@@ -338,12 +341,12 @@ static int fedavg_reduce_f32_impl(const float* const* rows, const float* weights
         const int grid = grid_for(n_vec, kReduceThreads, per_sm > 2 ? 2 : per_sm);
         fedavg_reduce_f32_kernel<true><<<grid, kReduceThreads, smem, s>>>(
             rows, weights, n_rows, old, old_scale, inv_total, table, n_dsts, mc_dst, lo, hi, peer_flags, n_ranks, rank,
-            epoch, nan_flag, g_done_counter[dev]);
+            epoch, nan_flag, done_slot);
     } else {
         const int grid = grid_for(n_vec, kReduceThreads, 4);
         fedavg_reduce_f32_kernel<false><<<grid, kReduceThreads, smem, s>>>(
             rows, weights, n_rows, old, old_scale, inv_total, table, n_dsts, nullptr, lo, hi, nullptr, 1, 0, 0, nan_flag,
-            nullptr);
+            0);
     }
     DLS_LAUNCHED("fedavg_reduce_f32_kernel");
     return 0;
