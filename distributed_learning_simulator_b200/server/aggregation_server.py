@@ -1,13 +1,16 @@
-"""Server that aggregates worker uploads once per round.
+"""Server that aggregates the workers' uploads once per round.
 
-Behaviour parity with /root/reference/simulation_lib/server/aggregation_server.py:15-184:
-initial-model distribution (``distribute_init_parameters``, warm start from
-``algorithm_kwargs.global_model_path``), per-round test metric into
-``round_record.json``, ``best_global_model.pk``, cached round model
-``aggregated_model/round_<n>.pk``, ``need_init_performance`` (stat key 0), early stop on a
-5-round plateau with a 0.001 improvement threshold, ``_get_stat_key`` override point.
-Fixed here: after broadcasting ``end_training`` the server stops (the reference keeps
-polling, SURVEY.md defect D8).
+What a run leaves behind and when it ends follows /root/reference/simulation_lib/server/aggregation_server.py:15-184:
+the initial model goes out first (``distribute_init_parameters``; warm start from ``algorithm_kwargs.global_model_path``),
+every aggregated model is evaluated on the test split into ``round_record.json``, the best one is kept as
+``best_global_model.pk``, the round's model is cached under ``aggregated_model/round_<n>.pk``, Shapley-style methods
+ask for the metric of the initial model (``need_init_performance``, stat key 0), and ``early_stop`` ends training on
+a 5-round plateau with a 0.001 threshold.  ``_get_stat_key`` stays an override point.  Not reproduced: the reference
+keeps polling after it has broadcast ``end_training`` (SURVEY.md defect D8); this server stops.
+
+The bookkeeping is split from the protocol: ``_RoundLedger`` owns the metric history, its files and the plateau
+rule; ``_CheckpointStore`` owns the round-counter checkpoint (an extension: ``algorithm_kwargs.checkpoint_interval`` /
+``resume_from``); ``AggregationServer`` is the protocol - collect one upload per worker, aggregate, publish.
 """
 import json
 import os
@@ -17,37 +20,129 @@ from typing import Any
 from ..algorithm.aggregation_algorithm import AggregationAlgorithm
 from ..engine.log import get_logger
 from ..engine.tensor import TensorDict, tensor_to
-from ..message import Message, ParameterMessage, ParameterMessageBase
+from ..message import FlatParameter, Message, ParameterMessage, ParameterMessageBase
 from ..util.model_cache import ModelCache
 from ..utils import tracing
+from ..utils.observer import notify_round_end
 from .server import Server
+
+_PLATEAU_ROUNDS = 5
+_PLATEAU_THRESHOLD = 0.001
+
+
+def _host_copy(parameter: TensorDict) -> dict:
+    return dict(tensor_to(dict(parameter), device="cpu"))
+
+
+class _RoundLedger:
+    """Test metrics per stat key, the files derived from them, and the early-stop rule."""
+
+    def __init__(self, save_dir: str) -> None:
+        self._save_dir = save_dir
+        self.records: dict = {}
+        self.best_saved = 0.0
+        self.plateau_reference = 0.0
+        self.plateau_length = 0
+
+    def best_accuracy(self) -> float:
+        return max(record["test_accuracy"] for record in self.records.values())
+
+    def write(self) -> None:
+        with open(os.path.join(self._save_dir, "round_record.json"), "wt", encoding="utf8") as f:
+            json.dump(self.records, f)
+
+    def add(self, key: int, metric: dict, parameter: TensorDict) -> None:
+        if key in self.records:
+            raise KeyError(f"round record {key} exists")
+        self.records[key] = {f"test_{name}": value for name, value in metric.items()}
+        self.write()
+        best = self.best_accuracy()
+        if best > self.best_saved:
+            self.best_saved = best
+            with open(os.path.join(self._save_dir, "best_global_model.pk"), "wb") as f:
+                pickle.dump(_host_copy(parameter), f)
+
+    def rename(self, old: int, new: int) -> None:
+        self.records[new] = self.records.pop(old)
+        self.write()
+
+    def on_plateau(self, current_key: int) -> bool:
+        """True once the best accuracy has not improved by more than the threshold for five checks in a row."""
+        best = self.best_accuracy()
+        if best > self.plateau_reference + _PLATEAU_THRESHOLD:
+            self.plateau_reference, self.plateau_length = best, 0
+            return False
+        self.plateau_length += 1
+        get_logger().warning("no improvement over %s for %s round(s); this round is %s below", self.plateau_reference,
+                             self.plateau_length, self.plateau_reference - self.records[current_key]["test_accuracy"])
+        return self.plateau_length >= _PLATEAU_ROUNDS
+
+    # what a checkpoint must carry to continue the history
+    def state(self) -> dict:
+        return {"stat": self.records, "plateau": self.plateau_length, "max_acc": self.plateau_reference,
+                "best_acc_saved": self.best_saved}
+
+    def restore(self, state: dict) -> None:
+        self.records = {int(key): value for key, value in state["stat"].items()}
+        self.plateau_length, self.plateau_reference = state["plateau"], state["max_acc"]
+        self.best_saved = state["best_acc_saved"]
+
+
+class _CheckpointStore:
+    """``server/checkpoint.pk``: round number, global model and ledger state, replaced atomically."""
+
+    def __init__(self, save_dir: str, interval: int) -> None:
+        self._save_dir, self.interval = save_dir, interval
+
+    @staticmethod
+    def path_in(save_dir: str) -> str:
+        return os.path.join(save_dir, "server", "checkpoint.pk")
+
+    def due(self, round_number: int) -> bool:
+        return self.interval > 0 and round_number % self.interval == 0
+
+    def save(self, round_number: int, parameter: TensorDict, ledger: _RoundLedger) -> None:
+        from ..parallel import context as parallel_context
+
+        ctx = parallel_context.current()
+        if ctx is not None and ctx.rank != 0:
+            return  # the replicas are identical: one writer
+        target = self.path_in(self._save_dir)
+        os.makedirs(os.path.dirname(target), exist_ok=True)
+        scratch = target + ".tmp"
+        with open(scratch, "wb") as f:
+            pickle.dump({"round": round_number, "parameter": _host_copy(parameter), **ledger.state()}, f)
+        os.replace(scratch, target)  # a crash mid-write leaves the previous checkpoint intact
+
+    @classmethod
+    def load(cls, location: str) -> dict:
+        if os.path.isdir(location):
+            location = cls.path_in(location)
+        with open(location, "rb") as f:
+            return pickle.load(f)
 
 
 class AggregationServer(Server):
     def __init__(self, algorithm: AggregationAlgorithm, **kwargs: Any) -> None:
-        Server.__init__(self, **kwargs)
-        self._model_cache: ModelCache = ModelCache()
-        self._round_number: int = 1
-        self.__worker_flag: set = set()
-        self.__algorithm: AggregationAlgorithm = algorithm
-        self.__stat: dict = {}
-        self._compute_stat: bool = True
-        self.__plateau = 0
-        self.__max_acc = 0.0
-        self.__best_acc_saved = 0.0
-        self.__end_training_sent = False
+        super().__init__(**kwargs)
+        options = self.config.algorithm_kwargs
+        self.__algorithm = algorithm
+        self.__reported: set = set()
+        self.__ledger = _RoundLedger(self.save_dir)
+        self.__checkpoints = _CheckpointStore(self.config.save_dir, int(options.get("checkpoint_interval", 0) or 0))
+        self.__early_stop = bool(options.get("early_stop", False))
+        self.__finished = False
+        self.__resume_model: TensorDict | None = None
+        self._model_cache = ModelCache()
+        self._round_number = 1
+        self._compute_stat = True
         self.need_init_performance = False
-        self.__early_stop = self.config.algorithm_kwargs.get("early_stop", False)
         if self.__early_stop:
-            get_logger().warning("stop early")
-        # extension over the reference (which only warm-starts from ``global_model_path``,
-        # aggregation_server.py:43-52): round-counter checkpoints and resume
-        self.__checkpoint_interval = int(self.config.algorithm_kwargs.get("checkpoint_interval", 0) or 0)
-        self.__resumed_parameter: TensorDict | None = None
-        resume_from = self.config.algorithm_kwargs.get("resume_from", None)
-        if resume_from:
-            self.__resume(resume_from)
+            get_logger().warning("training ends early on an accuracy plateau")
+        if options.get("resume_from"):
+            self.__continue_from(options["resume_from"])
 
+    # ---- facts -----------------------------------------------------------------------------------------
     @property
     def early_stop(self) -> bool:
         return self.__early_stop
@@ -60,81 +155,71 @@ class AggregationServer(Server):
     def round_number(self) -> int:
         return self._round_number
 
-    # ---- checkpoint / resume (extension) ----------------------------------------------------------
+    @property
+    def performance_stat(self) -> dict:
+        return self.__ledger.records
+
+    def _get_stat_key(self) -> int:
+        return self._round_number
+
+    def _stopped(self) -> bool:
+        return self.__finished or self._round_number > self.config.round
+
+    # ---- checkpoint / resume (extension over the reference) ----------------------------------------------
     @staticmethod
     def checkpoint_path(save_dir: str) -> str:
-        return os.path.join(save_dir, "server", "checkpoint.pk")
+        return _CheckpointStore.path_in(save_dir)
 
-    def __resume(self, path: str) -> None:
-        if os.path.isdir(path):
-            path = self.checkpoint_path(path)
-        with open(path, "rb") as f:
-            state = pickle.load(f)
+    def __continue_from(self, location: str) -> None:
+        state = _CheckpointStore.load(location)
+        self.__ledger.restore(state)
+        self.__resume_model = state["parameter"]
         self._round_number = int(state["round"]) + 1
-        self.__stat = {int(k): v for k, v in state["stat"].items()}
-        self.__plateau, self.__max_acc = state["plateau"], state["max_acc"]
-        self.__best_acc_saved = state["best_acc_saved"]
-        self.__resumed_parameter = state["parameter"]
-        get_logger().warning("resume from %s: continue with round %d of %d", path, self._round_number,
+        get_logger().warning("resume from %s: continue with round %d of %d", location, self._round_number,
                              self.config.round)
 
-    def __write_checkpoint(self, parameter: TensorDict) -> None:
-        from ..parallel import context as parallel_context
-
-        ctx = parallel_context.current()
-        if ctx is not None and ctx.rank != 0:
-            return  # server replicas are identical: one writer is enough
-        state = {"round": self._round_number, "stat": self.__stat, "plateau": self.__plateau,
-                 "max_acc": self.__max_acc, "best_acc_saved": self.__best_acc_saved,
-                 "parameter": dict(tensor_to(dict(parameter), device="cpu"))}
-        path = self.checkpoint_path(self.config.save_dir)
-        os.makedirs(os.path.dirname(path), exist_ok=True)
-        with open(path + ".tmp", "wb") as f:
-            pickle.dump(state, f)
-        os.replace(path + ".tmp", path)  # a crash mid-write leaves the previous checkpoint intact
-
+    # ---- first message ---------------------------------------------------------------------------------
     def _get_init_model(self) -> TensorDict:
-        if self.__resumed_parameter is not None:
-            return self.__resumed_parameter
-        init_global_model_path = self.config.algorithm_kwargs.get("global_model_path", None)
-        if init_global_model_path is not None:
-            with open(os.path.join(init_global_model_path), "rb") as f:
+        if self.__resume_model is not None:
+            return self.__resume_model
+        warm_start = self.config.algorithm_kwargs.get("global_model_path")
+        if warm_start is not None:
+            with open(warm_start, "rb") as f:
                 return pickle.load(f)
         tester = self.tester
         tester.set_device(self._get_device(), stream=self._server_stream())
-        from ..message import FlatParameter
-
-        flat = tester.model_util.flat_parameter
-        if flat is not None:
-            return FlatParameter(flat.detach().clone(), tester.model_util.layout)
-        return {k: v.clone() for k, v in tester.model_util.get_parameter_dict().items()}
+        util = tester.model_util
+        if util.flat_parameter is not None:
+            return FlatParameter(util.flat_parameter.detach().clone(), util.layout)
+        return {name: tensor.clone() for name, tensor in util.get_parameter_dict().items()}
 
     def _before_start(self) -> None:
-        if self.config.distribute_init_parameters:
-            other_data: dict = {"init": True}
-            if self.__resumed_parameter is not None:
-                other_data["resume_round"] = self._round_number  # workers continue their round counter
-            self._send_result(ParameterMessage(in_round=True, parameter=self._get_init_model(),
-                                               other_data=other_data))
-        else:
-            assert self.__resumed_parameter is None, "resume_from needs distribute_init_parameters"
+        if not self.config.distribute_init_parameters:
+            if self.__resume_model is not None:
+                raise ValueError("resume_from needs distribute_init_parameters")
+            return
+        tags: dict = {"init": True}
+        if self.__resume_model is not None:
+            tags["resume_round"] = self._round_number  # workers continue their own round counter
+        self._send_result(ParameterMessage(in_round=True, parameter=self._get_init_model(), other_data=tags))
 
     def _server_exit(self) -> None:
         self.__algorithm.exit()
 
+    # ---- collect -> aggregate -> publish -----------------------------------------------------------------
     def _process_worker_data(self, worker_id: int, data: Message | None) -> None:
-        assert 0 <= worker_id < self.worker_number
-        self.__algorithm.process_worker_data(
-            worker_id=worker_id, worker_data=data, save_dir=self.config.get_save_dir(),
-            old_parameter_dict=self._model_cache.parameter_dict)
-        self.__worker_flag.add(worker_id)
-        if len(self.__worker_flag) == self.worker_number:
-            result = self._aggregate_worker_data()
-            self._send_result(result)
-            self.__worker_flag.clear()
-        else:
-            get_logger().debug("we have %s committed, and we need %s workers,skip", len(self.__worker_flag),
-                               self.worker_number)
+        if not 0 <= worker_id < self.worker_number:
+            raise IndexError(f"worker id {worker_id} out of range")
+        self.__algorithm.process_worker_data(worker_id=worker_id, worker_data=data,
+                                             save_dir=self.config.get_save_dir(),
+                                             old_parameter_dict=self._model_cache.parameter_dict)
+        self.__reported.add(worker_id)
+        missing = self.worker_number - len(self.__reported)
+        if missing:
+            get_logger().debug("%s upload(s) in, waiting for %s more", len(self.__reported), missing)
+            return
+        self.__reported.clear()
+        self._send_result(self._aggregate_worker_data())
 
     def _aggregate_worker_data(self) -> Any:
         with tracing.phase("aggregate"):
@@ -143,31 +228,29 @@ class AggregationServer(Server):
     def _before_send_result(self, result: Message) -> None:
         if not isinstance(result, ParameterMessageBase):
             return
-        assert isinstance(result, ParameterMessage)
-        if self.need_init_performance:
-            assert self.config.distribute_init_parameters
-        if self.need_init_performance and "init" in result.other_data and "resume_round" not in result.other_data:
+        if not isinstance(result, ParameterMessage):
+            raise TypeError("the server publishes full models")
+        is_init = "init" in result.other_data
+        if is_init and self.need_init_performance and "resume_round" not in result.other_data:
+            if not self.config.distribute_init_parameters:
+                raise ValueError("need_init_performance needs distribute_init_parameters")
+            # metric of the initial model, filed under key 0 (the Shapley engines start from it)
             self._record_compute_stat(result.parameter, keep_performance_logger=False)
-            self.__stat[0] = self.__stat.pop(1)
-            self._dump_stat()
-        elif self._compute_stat and "init" not in result.other_data:
+            self.__ledger.rename(1, 0)
+        elif not is_init and self._compute_stat:
             self._record_compute_stat(result.parameter)
-            if not result.end_training and self.early_stop and self._convergent():
+            if self.early_stop and not result.end_training and self._convergent():
                 result.end_training = True
         elif result.end_training:
             self._record_compute_stat(result.parameter)
-        model_path = os.path.join(self.config.save_dir, "aggregated_model", f"round_{self.round_number}.pk")
-        self._model_cache.cache_parameter_dict(result.parameter, model_path)
-        if self.__checkpoint_interval > 0 and not result.in_round \
-                and self._round_number % self.__checkpoint_interval == 0:
-            self.__write_checkpoint(result.parameter)
-        if result.end_training:
-            self.__end_training_sent = True
+        self._model_cache.cache_parameter_dict(
+            result.parameter, os.path.join(self.config.save_dir, "aggregated_model", f"round_{self.round_number}.pk"))
+        if not result.in_round and self.__checkpoints.due(self._round_number):
+            self.__checkpoints.save(self._round_number, result.parameter, self.__ledger)
+        self.__finished = self.__finished or bool(result.end_training)
 
     def _after_send_result(self, result: Any) -> None:
         if isinstance(result, ParameterMessageBase) and not result.in_round:
-            from ..utils.observer import notify_round_end
-
             notify_round_end(self, self._round_number)
             self._round_number += 1
         self.__algorithm.clear_worker_data()
@@ -175,44 +258,15 @@ class AggregationServer(Server):
     def _after_unicast_result(self, result: Message) -> None:
         self.__algorithm.clear_worker_data()
 
-    def _stopped(self) -> bool:
-        return self._round_number > self.config.round or self.__end_training_sent
-
-    @property
-    def performance_stat(self) -> dict:
-        return self.__stat
-
-    def _get_stat_key(self) -> int:
-        return self._round_number
-
+    # ---- evaluation bookkeeping ------------------------------------------------------------------------
     def _dump_stat(self) -> None:
-        with open(os.path.join(self.save_dir, "round_record.json"), "wt", encoding="utf8") as f:
-            json.dump(self.__stat, f)
+        self.__ledger.write()
 
     def _record_compute_stat(self, parameter_dict: TensorDict, keep_performance_logger: bool = True) -> None:
         self.tester.set_visualizer_prefix(f"round: {self._round_number},")
         with tracing.phase("evaluate"):
             metric = self.get_metric(parameter_dict, keep_performance_logger=keep_performance_logger)
-        round_stat = {f"test_{k}": v for k, v in metric.items()}
-        key = self._get_stat_key()
-        assert key not in self.__stat
-        self.__stat[key] = round_stat
-        self._dump_stat()
-        max_acc = max(t["test_accuracy"] for t in self.__stat.values())
-        if max_acc > self.__best_acc_saved:
-            self.__best_acc_saved = max_acc
-            with open(os.path.join(self.save_dir, "best_global_model.pk"), "wb") as f:
-                pickle.dump(dict(tensor_to(dict(parameter_dict), device="cpu")), f)
+        self.__ledger.add(self._get_stat_key(), metric, parameter_dict)
 
     def _convergent(self) -> bool:
-        max_acc = max(t["test_accuracy"] for t in self.performance_stat.values())
-        diff = 0.001
-        if max_acc > self.__max_acc + diff:
-            self.__max_acc = max_acc
-            self.__plateau = 0
-            return False
-        get_logger().warning("max acc is %s diff is %s", self.__max_acc,
-                             self.__max_acc - self.performance_stat[self._get_stat_key()]["test_accuracy"])
-        self.__plateau += 1
-        get_logger().warning("plateau is %s", self.__plateau)
-        return self.__plateau >= 5
+        return self.__ledger.on_plateau(self._get_stat_key())
