@@ -1,8 +1,10 @@
-"""Worker side of FedDropoutAvg: full parameters, Bernoulli(1 - dropout_rate) element mask,
-``send_num`` / ``total_num`` log lines (scraped by analysis/analyze_log.py; reference:
-method/fed_dropout_avg/worker.py:10-30).  The mask, the product and the non-zero count
-are one kernel pass over the flat row (``ops.misc.dropout_mask``) instead of a Bernoulli
-tensor + multiply + ``count_nonzero().item()`` per parameter tensor."""
+"""Worker side of FedDropoutAvg: the full model goes up with a Bernoulli(1 - dropout_rate) element mask applied.
+
+Protocol and the two scrape-able log lines (``total_num`` / ``send_num``, read by analysis/analyze_log.py) follow
+/root/reference/simulation_lib/method/fed_dropout_avg/worker.py:10-30.  On the flat row the mask, the product and
+the count of surviving elements are one kernel pass (``ops.misc.dropout_mask``) rather than a Bernoulli tensor, a
+multiply and a ``count_nonzero().item()`` per parameter tensor.
+"""
 from typing import Any
 
 import torch
@@ -13,28 +15,34 @@ from ...ops import misc as misc_ops
 from ..common_import import AggregationWorker, ParameterMessage
 
 
+def _drop_elements(parameter: Any, keep_probability: float) -> tuple[Any, int, int]:
+    """``(masked parameter, elements in total, elements kept)``."""
+    flat = as_flat(parameter)
+    if flat is not None:
+        masked, kept = misc_ops.dropout_mask(flat.flat, keep_probability)
+        return FlatParameter(masked, flat.layout), flat.flat.numel(), int(kept.item())
+    masked_dict, total, kept_total = {}, 0, 0
+    for name, tensor in parameter.items():
+        survivors = torch.bernoulli(torch.full_like(tensor, keep_probability))
+        masked_dict[name] = tensor * survivors
+        total += tensor.numel()
+        kept_total += int(torch.count_nonzero(masked_dict[name]).item())
+    return masked_dict, total, kept_total
+
+
 class FedDropoutAvgWorker(AggregationWorker):
     def __init__(self, **kwargs: Any) -> None:
         super().__init__(**kwargs)
-        self.__dropout_rate: float = self.config.algorithm_kwargs["dropout_rate"]
-        get_logger().warning("use dropout_rate %s", self.__dropout_rate)
+        self._send_parameter_diff = False  # the server needs absolute values: zero means "dropped"
+        self.__keep_probability = 1.0 - float(self.config.algorithm_kwargs["dropout_rate"])
+        get_logger().warning("use dropout_rate %s", 1.0 - self.__keep_probability)
 
     def _get_sent_data(self) -> ParameterMessage:
         self._send_parameter_diff = False
-        sent_data = super()._get_sent_data()
-        assert isinstance(sent_data, ParameterMessage)
-        keep = 1.0 - self.__dropout_rate
-        flat = as_flat(sent_data.parameter)
-        if flat is not None:
-            masked, count = misc_ops.dropout_mask(flat.flat, keep)
-            sent_data.parameter = FlatParameter(masked, flat.layout)
-            total_num, send_num = flat.flat.numel(), int(count.item())
-        else:
-            total_num = send_num = 0
-            for k, v in sent_data.parameter.items():
-                sent_data.parameter[k] = v * torch.bernoulli(torch.full_like(v, keep))
-                total_num += v.numel()
-                send_num += int(torch.count_nonzero(sent_data.parameter[k]).item())
-        get_logger().warning("total_num %s", total_num)
-        get_logger().warning("send_num %s", send_num)
-        return sent_data
+        upload = super()._get_sent_data()
+        if not isinstance(upload, ParameterMessage):
+            raise TypeError("FedDropoutAvg uploads full models")
+        upload.parameter, total, kept = _drop_elements(upload.parameter, self.__keep_probability)
+        get_logger().warning("total_num %s", total)
+        get_logger().warning("send_num %s", kept)
+        return upload

@@ -1,6 +1,9 @@
-"""Client: a worker that talks to a server through its endpoint
-(/root/reference/simulation_lib/worker/client.py:9-22).  Waiting for the server blocks on
-the endpoint's condition variable instead of the reference's 0.1 s polling loop."""
+"""Client: a worker with a line to a server (role of /root/reference/simulation_lib/worker/client.py:9-22).
+
+``send_data_to_server`` hands a message to the endpoint; ``_get_data_from_server`` sleeps on the endpoint's condition
+variable until the answer is there - no 0.1 s polling loop - and gives up after ``config.round_timeout`` seconds so a
+dead server becomes an error.
+"""
 from typing import Any
 
 from ..engine.device import capture_guard
@@ -13,10 +16,11 @@ class Client(Worker):
 
     def _get_data_from_server(self) -> Any:
         self._release_device_lock()
-        timeout = getattr(self.config, "round_timeout", None)
-        # a worker that waits inside an eager section (the graph workers exchange embeddings from forward
-        # hooks) must not keep the capture guard: another role's graph capture may be what everybody waits for
+        patience = getattr(self.config, "round_timeout", None)
+        # A worker may wait from inside an eager section (the graph workers exchange embeddings from forward hooks).
+        # It must not sit on the capture guard meanwhile: the capture of another role may be what everybody waits for.
         with capture_guard.released():
-            if not self._endpoint.wait_for_data(timeout=timeout):
-                raise TimeoutError(f"{self.name}: no answer from the server within {timeout}s")
+            answered = self._endpoint.wait_for_data(timeout=patience)
+        if not answered:
+            raise TimeoutError(f"{self.name}: no answer from the server within {patience}s")
         return self._endpoint.get()
