@@ -352,7 +352,9 @@ __device__ __forceinline__ void wide_block_fold(int cv, const float (&a)[V], con
     }
 }
 
-template <typename T, int V, bool kBackward>
+// kAtomic: the CTA adds its partial sums to `partials` ([2][channels], zeroed by the caller) with atomics instead of
+// folding them across a cluster: no cluster barriers, no DSMEM reads, and the apply kernel reads one partial.
+template <typename T, int V, bool kBackward, bool kAtomic = false>
 __global__ void __launch_bounds__(kWideThreads)
 bn_wide_reduce_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T* __restrict__ y, long long rows,
                       int channels, const float* __restrict__ mean, const float* __restrict__ invstd, int relu,
@@ -399,6 +401,14 @@ bn_wide_reduce_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T
         }
     }
     wide_block_fold<V>(cv, a, b, s_buf, s_part, channels);
+    if (kAtomic) {
+        __syncthreads();
+        for (int j = threadIdx.x; j < 2 * channels; j += kWideThreads) {
+            const float v = s_part[j];
+            if (v != 0.f) atomicAdd(partials + j, v);
+        }
+        return;
+    }
     cluster.sync();
     if (cluster.block_rank() == 0) {
         const unsigned int size = cluster.num_blocks();
@@ -558,17 +568,25 @@ static cudaError_t bn_wide_fwd(const void* x, long long rows, int channels, cons
 template <typename T, int V>
 static cudaError_t bn_wide_bwd(const void* dy, const void* y, const void* x, long long rows, int channels,
                                const float* gamma, const float* mean, const float* invstd, int relu, void* dx,
-                               void* dresidual, float* dgamma, float* dbeta, float* scratch, cudaStream_t s) {
+                               void* dresidual, float* dgamma, float* dbeta, float* scratch, float* zeroed,
+                               cudaStream_t s) {
     const int clusters = bn_wide_clusters(rows, channels, V);
     const size_t smem1 = (size_t)(kWideThreads * 2 * V + 2 * channels) * sizeof(float);
-    cudaError_t e = wide_launch(bn_wide_reduce_kernel<T, V, true>, clusters * kWideCluster, kWideCluster, smem1, s,
-                                (const T*)x, (const T*)dy, (const T*)y, rows, channels, mean, invstd, relu, scratch);
+    cudaError_t e;
+    if (zeroed != nullptr) {
+        e = wide_launch(bn_wide_reduce_kernel<T, V, true, true>, clusters * kWideCluster, 1, smem1, s, (const T*)x,
+                        (const T*)dy, (const T*)y, rows, channels, mean, invstd, relu, zeroed);
+    } else {
+        e = wide_launch(bn_wide_reduce_kernel<T, V, true>, clusters * kWideCluster, kWideCluster, smem1, s,
+                        (const T*)x, (const T*)dy, (const T*)y, rows, channels, mean, invstd, relu, scratch);
+    }
     if (e != cudaSuccess) return e;
     g_launch_count.fetch_add(1);
     const int grid2 = (int)((rows + (kWideThreads / (channels / V)) * 4 - 1) / ((kWideThreads / (channels / V)) * 4));
     return wide_launch(bn_wide_apply_kernel<T, V, true>, grid2 > 2 * kNumSMs ? 2 * kNumSMs : grid2, 1,
                        (size_t)2 * channels * sizeof(float), s, (const T*)x, (const T*)dy, (const T*)y, rows,
-                       channels, gamma, (const float*)nullptr, 0.f, relu, (const float*)scratch, clusters,
+                       channels, gamma, (const float*)nullptr, 0.f, relu,
+                       (const float*)(zeroed != nullptr ? zeroed : scratch), zeroed != nullptr ? 1 : clusters,
                        const_cast<float*>(mean), const_cast<float*>(invstd), dgamma, dbeta, (T*)dx, (T*)dresidual);
 }
 
@@ -709,19 +727,19 @@ extern "C" int dls_bn_fwd_stats(const void* x, int dtype, long long rows, int ch
     return 0;
 }
 
-extern "C" int dls_bn_bwd(const void* dy, const void* y, const void* x, int dtype, long long rows, int channels,
-                          const float* gamma, const float* mean, const float* invstd, int relu, void* dx,
-                          void* dresidual, float* dgamma, float* dbeta, float* scratch, void* stream) {
+static int bn_bwd_impl(const void* dy, const void* y, const void* x, int dtype, long long rows, int channels,
+                       const float* gamma, const float* mean, const float* invstd, int relu, void* dx,
+                       void* dresidual, float* dgamma, float* dbeta, float* scratch, float* zeroed, void* stream) {
     BnPlan p;
     if (int rc = bn_plan(rows, channels, dtype, &p)) return rc;
     if (relu && y == nullptr) return fail_msg("bn bwd: the forward output is needed for the ReLU mask");
     cudaStream_t s = (cudaStream_t)stream;
     cudaError_t e;
     if (bn_use_wide(rows, channels, p.v)) {
-        if (scratch == nullptr) return fail_msg("dls_bn_bwd: this shape needs the scratch buffer");
-        if (dtype == 1 && p.v == 8) e = bn_wide_bwd<__nv_bfloat16, 8>(dy, y, x, rows, channels, gamma, mean, invstd, relu, dx, dresidual, dgamma, dbeta, scratch, s);
-        else if (dtype == 1) e = bn_wide_bwd<__nv_bfloat16, 4>(dy, y, x, rows, channels, gamma, mean, invstd, relu, dx, dresidual, dgamma, dbeta, scratch, s);
-        else e = bn_wide_bwd<float, 4>(dy, y, x, rows, channels, gamma, mean, invstd, relu, dx, dresidual, dgamma, dbeta, scratch, s);
+        if (scratch == nullptr && zeroed == nullptr) return fail_msg("dls_bn_bwd: this shape needs the scratch buffer");
+        if (dtype == 1 && p.v == 8) e = bn_wide_bwd<__nv_bfloat16, 8>(dy, y, x, rows, channels, gamma, mean, invstd, relu, dx, dresidual, dgamma, dbeta, scratch, zeroed, s);
+        else if (dtype == 1) e = bn_wide_bwd<__nv_bfloat16, 4>(dy, y, x, rows, channels, gamma, mean, invstd, relu, dx, dresidual, dgamma, dbeta, scratch, zeroed, s);
+        else e = bn_wide_bwd<float, 4>(dy, y, x, rows, channels, gamma, mean, invstd, relu, dx, dresidual, dgamma, dbeta, scratch, zeroed, s);
         if (e != cudaSuccess) return fail("bn_wide_bwd", e);
         DLS_LAUNCHED("bn_wide_apply_kernel");
         return 0;
@@ -744,4 +762,22 @@ extern "C" int dls_bn_bwd(const void* dy, const void* y, const void* x, int dtyp
     if (e != cudaSuccess) return fail("bn_bwd_kernel", e);
     DLS_LAUNCHED("bn_bwd_kernel");
     return 0;
+}
+
+extern "C" int dls_bn_bwd(const void* dy, const void* y, const void* x, int dtype, long long rows, int channels,
+                          const float* gamma, const float* mean, const float* invstd, int relu, void* dx,
+                          void* dresidual, float* dgamma, float* dbeta, float* scratch, void* stream) {
+    return bn_bwd_impl(dy, y, x, dtype, rows, channels, gamma, mean, invstd, relu, dx, dresidual, dgamma, dbeta, scratch,
+                       nullptr, stream);
+}
+
+// Same, for callers that own a zeroed fp32 [2][channels] buffer (e.g. a slice of a per-step arena cleared by one
+// fill): on the row-major shapes the reduction pass adds its partial sums there with atomics and the apply pass
+// reads that single partial - no cluster fold.  Shapes on the channel-major path ignore the buffer.
+extern "C" int dls_bn_bwd_acc(const void* dy, const void* y, const void* x, int dtype, long long rows, int channels,
+                              const float* gamma, const float* mean, const float* invstd, int relu, void* dx,
+                              void* dresidual, float* dgamma, float* dbeta, float* zeroed_partials, void* stream) {
+    if (zeroed_partials == nullptr) return fail_msg("dls_bn_bwd_acc: needs the zeroed partial-sum buffer");
+    return bn_bwd_impl(dy, y, x, dtype, rows, channels, gamma, mean, invstd, relu, dx, dresidual, dgamma, dbeta, nullptr,
+                       zeroed_partials, stream);
 }

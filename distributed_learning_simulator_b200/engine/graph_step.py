@@ -81,7 +81,9 @@ class GraphTrainStep:
         if n_convs > 0 and os.environ.get("DLS_SPLIT_BACKWARD", "1") != "0":
             self.side_stream = torch.cuda.Stream(device=self.device)
         self.grad_flags: torch.Tensor | None = None
-        stats_floats = sum(2 * m.out_channels for m in trainer.model.modules() if type(m) is torch.nn.Conv2d)
+        # per step: [2][Cout] for every convolution's statistics epilogue + [2][C] for every BatchNorm's backward sums
+        stats_floats = sum(2 * m.out_channels for m in trainer.model.modules() if type(m) is torch.nn.Conv2d) + \
+            sum(2 * m.num_features for m in trainer.model.modules() if isinstance(m, torch.nn.BatchNorm2d))
         self.stats_buf = torch.zeros(stats_floats, dtype=torch.float32, device=self.device) if stats_floats else None
         # state: [0] lr/optimizer step, [1] momentum initialised, [2] batch index in epoch
         self.state = torch.zeros(4, dtype=torch.int32, device=self.device)

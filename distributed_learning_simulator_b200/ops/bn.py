@@ -11,7 +11,7 @@ from torch import nn
 from . import runtime
 
 _DTYPE = {torch.float32: 0, torch.bfloat16: 1}
-STATS = {"fused_fwd": 0, "fused_stats": 0, "fallback": 0}
+STATS = {"fused_fwd": 0, "fused_stats": 0, "fallback": 0, "bwd_acc": 0}
 
 
 def _enabled() -> bool:
@@ -33,6 +33,9 @@ def can_fuse(bn: nn.Module, x: torch.Tensor, residual: torch.Tensor | None) -> b
                                  or not residual.is_contiguous(memory_format=torch.channels_last)):
         return False
     return True
+
+
+_BWD_ACC = os.environ.get("DLS_BN_BWD_ACC", "1") != "0"
 
 
 def _scratch(rows: int, channels: int, dtype: int, device: torch.device) -> torch.Tensor | None:
@@ -62,6 +65,13 @@ class _FusedBNAct(torch.autograd.Function):
                          runtime.ptr(residual), float(eps), int(relu), y.data_ptr(), mean.data_ptr(),
                          invstd.data_ptr(), runtime.ptr(scratch), runtime.stream_ptr(x.device))
         STATS["fused_fwd"] += 1
+        # row-major shapes: a zeroed slice of the step's arena lets the backward reduction add its partial sums with
+        # atomics instead of folding them across a cluster (csrc/bn.cu, dls_bn_bwd_acc)
+        ctx.bwd_partials = None
+        if _BWD_ACC and any(ctx.needs_input_grad[:3]) and runtime.require().dls_bn_scratch_floats(rows, c, dtype) > 0:
+            from . import conv as conv_ops
+
+            ctx.bwd_partials = conv_ops.take_arena_slice(2 * c)
         ctx.save_for_backward(x, y if relu else x, weight, mean, invstd)
         ctx.relu, ctx.has_residual, ctx.bn = bool(relu), residual is not None, bn
         return y
@@ -78,6 +88,13 @@ class _FusedBNAct(torch.autograd.Function):
         dres = torch.empty_like(x) if ctx.has_residual else None
         dgamma = torch.empty(c, dtype=torch.float32, device=x.device)
         dbeta = torch.empty(c, dtype=torch.float32, device=x.device)
+        if ctx.bwd_partials is not None:
+            runtime.call("dls_bn_bwd_acc", dy.data_ptr(), y.data_ptr(), x.data_ptr(), dtype, rows, c, weight.data_ptr(),
+                         mean.data_ptr(), invstd.data_ptr(), int(ctx.relu), dx.data_ptr(), runtime.ptr(dres),
+                         dgamma.data_ptr(), dbeta.data_ptr(), ctx.bwd_partials.data_ptr(),
+                         runtime.stream_ptr(x.device))
+            STATS["bwd_acc"] += 1
+            return dx, dgamma, dbeta, dres, None, None, None, None
         scratch = _scratch(rows, c, dtype, x.device)
         runtime.call("dls_bn_bwd", dy.data_ptr(), y.data_ptr(), x.data_ptr(), dtype, rows, c, weight.data_ptr(),
                      mean.data_ptr(), invstd.data_ptr(), int(ctx.relu), dx.data_ptr(), runtime.ptr(dres),

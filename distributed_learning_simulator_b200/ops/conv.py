@@ -172,6 +172,19 @@ def take_stats(channels: int, device: torch.device) -> torch.Tensor:
     return torch.zeros(2, channels, dtype=torch.float32, device=device)
 
 
+def take_arena_slice(floats: int) -> "torch.Tensor | None":
+    """``floats`` zeroed fp32 values from the open per-step arena, or None when no arena is open / it is exhausted
+    (callers then fall back to a path that needs no pre-zeroed memory)."""
+    arena = getattr(_tls, "stats_arena", None)
+    if arena is None:
+        return None
+    buf, used = arena
+    if used + floats > buf.numel():
+        return None
+    arena[1] = used + floats
+    return buf[used: used + floats]
+
+
 class _Conv2d(torch.autograd.Function):
     """mode 1 = tensor cores, 2 = direct, 3 = stem (explicit patches + tensor cores).  ``sink``: persistent
     fp32 buffer in the filter's physical layout that receives the weight gradient instead of ``weight.grad``

@@ -70,6 +70,8 @@ _SIGNATURES = {
                          c_void_p, c_void_p, c_void_p],
     "dls_bn_bwd": [c_void_p, c_void_p, c_void_p, c_int, c_ll, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p,
                    c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+    "dls_bn_bwd_acc": [c_void_p, c_void_p, c_void_p, c_int, c_ll, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p,
+                       c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
     "dls_sign_pack": [c_void_p, c_ll, c_void_p, c_void_p],
     "dls_sign_majority": [c_void_p, c_int, c_ll, c_void_p, c_void_p],
     "dls_sign_vote_sgd": [c_void_p, c_int, c_ll, c_void_p, c_void_p, c_float, c_float, c_float, c_int, c_int, c_void_p,

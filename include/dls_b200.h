@@ -117,6 +117,11 @@ int dls_bn_fwd_stats(const void* x, int dtype, long long rows, int channels, con
 int dls_bn_bwd(const void* dy, const void* y, const void* x, int dtype, long long rows, int channels,
                const float* gamma, const float* mean, const float* invstd, int relu, void* dx, void* dresidual,
                float* dgamma, float* dbeta, float* scratch, void* stream);
+/* dls_bn_bwd for callers that own a ZEROED fp32 [2][channels] buffer (one slice of an arena cleared once per step):
+ * the row-major path adds its partial sums there with atomics instead of folding them across a cluster. */
+int dls_bn_bwd_acc(const void* dy, const void* y, const void* x, int dtype, long long rows, int channels,
+                   const float* gamma, const float* mean, const float* invstd, int relu, void* dx, void* dresidual,
+                   float* dgamma, float* dbeta, float* zeroed_partials, void* stream);
 
 /* ---- bf16 GEMM on tcgen05 tensor cores, TMEM accumulators, TMA operand loads ------------
  *      (reference: torch.nn.Linear inside the external Inferencer, server/server.py:40-55, and

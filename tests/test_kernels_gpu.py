@@ -313,8 +313,14 @@ def test_block_sqdiff(dev):
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
 @pytest.mark.parametrize("shape", [(64, 64, 32, 32), (7, 24, 5, 3), (3, 512, 4, 4), (16, 36, 8, 8), (16, 36, 32, 32)])
 @pytest.mark.parametrize("relu,with_res", [(True, False), (True, True), (False, False)])
-def test_fused_bn_act_matches_pytorch(dev, dtype, shape, relu, with_res):
+@pytest.mark.parametrize("arena", [False, True])
+def test_fused_bn_act_matches_pytorch(dev, dtype, shape, relu, with_res, arena):
+    """``arena``: the forward runs inside a per-step statistics arena, so the row-major shapes take the backward
+    that adds its partial sums into a zeroed arena slice (dls_bn_bwd_acc) instead of folding them over a cluster."""
+    import contextlib
+
     from distributed_learning_simulator_b200.ops import bn as B
+    from distributed_learning_simulator_b200.ops import conv as C
 
     n, c, h, w = shape
     g = torch.Generator(device="cuda").manual_seed(c + h)
@@ -329,8 +335,13 @@ def test_fused_bn_act_matches_pytorch(dev, dtype, shape, relu, with_res):
     x1 = x.clone().requires_grad_(True)
     r1 = res.clone().requires_grad_(True) if with_res else None
     assert B.can_fuse(bn, x1, r1)
-    y = B.bn_act(bn, x1, relu=relu, residual=r1)
+    acc_before = B.STATS["bwd_acc"]
+    slab = torch.zeros(4 * c, dtype=torch.float32, device=dev)
+    with (C.stats_arena(slab) if arena else contextlib.nullcontext()):
+        y = B.bn_act(bn, x1, relu=relu, residual=r1)
     y.backward(dy)
+    row_major = n * h * w >= 8192 and c // (8 if dtype == torch.bfloat16 and c % 8 == 0 else 4) <= 128
+    assert (B.STATS["bwd_acc"] == acc_before + 1) == (arena and row_major)
     got = (y, x1.grad, bn.weight.grad.clone(), bn.bias.grad.clone(), r1.grad if with_res else None)
     bn.zero_grad()
     x2 = x.float().clone().requires_grad_(True)
