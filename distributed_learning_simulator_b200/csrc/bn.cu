@@ -517,8 +517,12 @@ bn_wide_apply_kernel(const T* __restrict__ x, const T* __restrict__ aux, const T
 // the threads of a CTA that do not fit a whole number of rows stay idle)
 static bool bn_use_wide(long long rows, int channels, int v) {
     static const bool disabled = [] { const char* e = getenv("DLS_BN_WIDE"); return e && e[0] == '0'; }();
+    static const long long min_rows = [] {
+        const char* e = getenv("DLS_BN_WIDE_MIN_ROWS");
+        return e ? atoll(e) : 8192LL;
+    }();
     const int cv = channels / v;
-    return !disabled && cv <= 128 && rows >= 8192;
+    return !disabled && cv <= 128 && rows >= min_rows;
 }
 static int bn_wide_clusters(long long rows, int channels, int v) {
     const int rows_per_iter = kWideThreads / (channels / v);
