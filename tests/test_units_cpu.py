@@ -133,3 +133,47 @@ def test_random_label_iid_split_covers_every_label_and_partitions_the_samples():
         assert len(labels) <= 4
         labels_seen |= labels
     assert labels_seen == set(range(10))
+
+
+def test_round_ledger_files_plateau_rule_and_checkpoint_round_trip(tmp_path):
+    """The aggregation server's bookkeeping on its own (server/aggregation_server.py): ``round_record.json`` follows
+    every record, the best model is rewritten only on improvement, the initial-model record moves to key 0, the
+    early-stop rule fires after five checks without a 0.001 improvement (reference aggregation_server.py:160-184),
+    and a checkpoint restores the history."""
+    import json
+    import pickle
+
+    import torch
+
+    from distributed_learning_simulator_b200.server.aggregation_server import _CheckpointStore, _RoundLedger
+
+    ledger = _RoundLedger(str(tmp_path))
+    model = {"w": torch.ones(3)}
+    ledger.add(1, {"accuracy": 0.10, "loss": 2.0}, model)
+    ledger.rename(1, 0)                                   # metric of the initial model (need_init_performance)
+    assert json.load(open(tmp_path / "round_record.json")) == {"0": {"test_accuracy": 0.10, "test_loss": 2.0}}
+    assert pickle.load(open(tmp_path / "best_global_model.pk", "rb"))["w"].tolist() == [1.0, 1.0, 1.0]
+    ledger.add(1, {"accuracy": 0.50, "loss": 1.0}, {"w": torch.full((3,), 2.0)})
+    assert pickle.load(open(tmp_path / "best_global_model.pk", "rb"))["w"][0] == 2.0
+    assert ledger.on_plateau(1) is False                  # 0.50 is an improvement over the initial reference 0
+    fired = []
+    for key in range(2, 8):
+        ledger.add(key, {"accuracy": 0.5005, "loss": 1.0}, {"w": torch.full((3,), float(key))})
+        fired.append(ledger.on_plateau(key))
+    assert fired == [False, False, False, False, True, True]   # five flat checks in a row
+    assert pickle.load(open(tmp_path / "best_global_model.pk", "rb"))["w"][0] == 2.0   # 0.5005 first seen at key 2
+    try:
+        ledger.add(3, {"accuracy": 0.9, "loss": 0.1}, model)
+        raise AssertionError("a round is recorded once")
+    except KeyError:
+        pass
+
+    store = _CheckpointStore(str(tmp_path), interval=2)
+    assert [r for r in range(1, 7) if store.due(r)] == [2, 4, 6] and not _CheckpointStore(str(tmp_path), 0).due(4)
+    store.save(4, {"w": torch.arange(3.0)}, ledger)
+    state = _CheckpointStore.load(str(tmp_path))          # a directory resolves to server/checkpoint.pk
+    assert state["round"] == 4 and state["parameter"]["w"].tolist() == [0.0, 1.0, 2.0]
+    restored = _RoundLedger(str(tmp_path / "elsewhere"))
+    restored.restore(state)
+    assert restored.records == ledger.records and restored.plateau_length == ledger.plateau_length
+    assert restored.best_saved == ledger.best_saved
