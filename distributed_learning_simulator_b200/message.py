@@ -53,33 +53,23 @@ class DeltaParameterMessage(ParameterMessageBase):
     delta_parameter: TensorDict
 
     def restore(self, parameter: TensorDict) -> ParameterMessage:
-        old_flat, delta_flat = as_flat(parameter), as_flat(self.delta_parameter)
-        if old_flat is not None and delta_flat is not None and old_flat.layout == delta_flat.layout:
-            new_parameter: TensorDict = FlatParameter(
-                old_flat.flat + delta_flat.flat.to(old_flat.flat.device), old_flat.layout)
+        """The full model ``parameter + delta`` as a ParameterMessage that keeps every other field of this one."""
+        base, delta = as_flat(parameter), as_flat(self.delta_parameter)
+        if base is not None and delta is not None and base.layout == delta.layout:
+            # one fused add over the whole row
+            summed: TensorDict = FlatParameter(base.flat + delta.flat.to(base.flat.device), base.layout)
         else:
-            new_parameter = {}
-        for k, v in ([] if new_parameter else parameter.items()):
-            d = self.delta_parameter.get(k)
-            new_parameter[k] = v + d.to(v.device) if d is not None else v
-        msg = ParameterMessage(parameter=new_parameter)
-        for f in fields(self):
-            if f.name != "delta_parameter":
-                setattr(msg, f.name, getattr(self, f.name))
-        msg.parameter = new_parameter
-        return msg
+            summed = {name: (old + self.delta_parameter[name].to(old.device) if name in self.delta_parameter else old)
+                      for name, old in parameter.items()}
+        carried = {f.name: getattr(self, f.name) for f in fields(self) if f.name != "delta_parameter"}
+        return ParameterMessage(parameter=summed, **carried)
 
 
 def get_message_size(msg: Any) -> int:
-    cnt: int = 0
-    seen: set[int] = set()
-
-    def count(data: torch.Tensor) -> None:
-        nonlocal cnt
-        if id(data) not in seen:
-            seen.add(id(data))
-            cnt += data.element_size() * data.numel()
-
-    for_each_tensor(msg, count)
-    assert cnt > 0
-    return cnt
+    """Payload bytes of a message: every distinct tensor object reachable from it counted once."""
+    sizes: dict[int, int] = {}
+    for_each_tensor(msg, lambda t: sizes.setdefault(id(t), t.element_size() * t.numel()))
+    total = sum(sizes.values())
+    if total <= 0:
+        raise ValueError("the message carries no tensor")
+    return total
