@@ -177,3 +177,51 @@ def test_round_ledger_files_plateau_rule_and_checkpoint_round_trip(tmp_path):
     restored.restore(state)
     assert restored.records == ledger.records and restored.plateau_length == ledger.plateau_length
     assert restored.best_saved == ledger.best_saved
+
+
+def test_server_listening_loop_sweep_modes_and_watchdog():
+    """``Server._listen`` (server/server.py) with a scripted endpoint: in one-message-per-sweep mode a worker that has
+    already been heard is not listened to again until the sweep is complete; in any-time mode (sign_SGD) everybody is
+    expected on every wait; an empty wait raises instead of spinning (reference server.py:64-85 polls for ever)."""
+    import pytest
+
+    from distributed_learning_simulator_b200.server.server import Server
+
+    class _Endpoint:
+        worker_num = 3
+
+        def __init__(self, script):
+            self.script, self.asked = list(script), []
+
+        def wait_for_data(self, expected, timeout=None):
+            self.asked.append(sorted(expected))
+            return self.script.pop(0) if self.script else set()
+
+        def get(self, worker_id):
+            return f"m{worker_id}"
+
+    def listener(script, per_sweep, stop_after):
+        server = Server.__new__(Server)                       # the loop needs only these attributes
+        server._endpoint = _Endpoint(script)
+        server._one_message_per_sweep = per_sweep
+        server._Executor__config = type("C", (), {"worker_number": 3, "round_timeout": 5})()
+        heard: list = []
+        server._stopped = lambda: len(heard) >= stop_after
+        return server, heard
+
+    server, heard = listener([{2}, {0, 1}, {1}], per_sweep=True, stop_after=4)
+    for worker_id, message in server._listen():
+        heard.append((worker_id, message))
+    assert heard == [(2, "m2"), (0, "m0"), (1, "m1"), (1, "m1")]
+    assert server._endpoint.asked == [[0, 1, 2], [0, 1], [0, 1, 2]]   # worker 2 is not awaited twice in a sweep
+
+    server, heard = listener([{2}, {2}, {0}], per_sweep=False, stop_after=3)
+    for worker_id, message in server._listen():
+        heard.append((worker_id, message))
+    assert [w for w, _ in heard] == [2, 2, 0] and server._endpoint.asked == [[0, 1, 2]] * 3
+
+    server, heard = listener([{0}], per_sweep=True, stop_after=9)
+    with pytest.raises(TimeoutError):
+        for worker_id, message in server._listen():
+            heard.append((worker_id, message))
+    assert heard == [(0, "m0")]
