@@ -19,4 +19,11 @@ if __name__ == "__main__":
         "algorithm_kwargs": {"second_phase_epoch": 1, "dropout_rate": 0.3, "random_client_number": w},
         "dataset_kwargs": {"train_size": 256 * w, "test_size": 1000},
     }))
+    import torch
+
+    if torch.cuda.is_available():
+        free, total = torch.cuda.mem_get_info()
+        print(f"workers {w}: device memory in use {(total - free) / 2**30:.1f} GiB of {total / 2**30:.0f} GiB, "
+              f"torch reserved {torch.cuda.memory_reserved() / 2**30:.1f} GiB, "
+              f"peak allocated {torch.cuda.max_memory_allocated() / 2**30:.1f} GiB")
     print("done")
