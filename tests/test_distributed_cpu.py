@@ -143,3 +143,22 @@ def test_a_dead_worker_takes_the_whole_job_down(tmp_path):
     assert res.returncode != 0
     assert time.monotonic() - start < 200
     assert "injected fault" in res.stderr + res.stdout
+
+
+def test_many_packed_workers_per_rank(tmp_path):
+    """The ``large_scale`` shape in miniature: 24 workers as threads behind two ranks (12 per process), FedOBD with
+    its two phases and quantized uploads.  Both replicas must finish and agree; the same run with 100 workers
+    (50 threads per process) completes as well but is too slow for the suite."""
+    conf = {**_TINY, "distributed_algorithm": "fed_obd", "worker_number": 24, "round": 2, "log_level": "WARNING",
+            "dataset_kwargs": {"train_size": 24 * 64, "test_size": 160},
+            "endpoint_kwargs": {"server": {"weight": 0.01}, "worker": {"weight": 0.01}},
+            "algorithm_kwargs": {"dropout_rate": 0.3, "random_client_number": 24, "second_phase_epoch": 1}}
+    script = tmp_path / "packed.py"
+    script.write_text(MULTI_SCRIPT.format(root=ROOT, confs={"fed_obd": conf}, out=str(tmp_path)))
+    env = dict(os.environ, DLS_FORCE_CPU="1", DLS_OUTPUT_ROOT=str(tmp_path), OMP_NUM_THREADS="1")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), str(script)]
+    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=420)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    r0, r1 = (json.load(open(tmp_path / f"multi_{r}.json")) for r in range(2))
+    assert r0 == r1 and len(r0["fed_obd"]) >= 3      # two stage-one rounds and at least one stage-two record
