@@ -79,11 +79,11 @@ def launch_table(path: str, top: int = 30) -> str:
 def events_table(path: str) -> str:
     data = json.load(open(path))
     sustained = PEAKS.get("bf16_tflops_sustained", BF16)
-    out = [f"| kernel / size | us | GB/s | of measured copy peak ({HBM} GB/s) | TFLOP/s | of measured bf16 peak "
-           f"({BF16} burst / {sustained} sustained) |", "|---|---|---|---|---|---|"]
+    out = [f"| kernel / size | us (device) | us (eager call incl. Python wrapper) | GB/s | of measured copy peak ({HBM} GB/s) | "
+           f"TFLOP/s | of measured bf16 peak ({BF16} burst / {sustained} sustained) |", "|---|---|---|---|---|---|---|"]
     for name, e in data.items():
         gbs, tf = e.get("GB/s"), e.get("TFLOP/s")
-        out.append(f"| {name} | {e['us']} | {gbs if gbs is not None else '-'} | "
+        out.append(f"| {name} | {e['us']} | {e.get('us_eager', '-')} | {gbs if gbs is not None else '-'} | "
                    f"{(f'{gbs / HBM:.2f}' if gbs is not None else '-')} | {tf if tf is not None else '-'} | "
                    f"{(f'{tf / BF16:.2f} / {tf / sustained:.2f}' if tf is not None else '-')} |")
     return "\n".join(out)

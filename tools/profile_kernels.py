@@ -28,7 +28,57 @@ flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > L2 (126 MB)
 results = {}
 
 
-def timed(name, fn, bytes_moved=None, flops=None, cold=True):
+GRAPH_REPS = 10
+
+
+def _replay_us(graph):
+    graph.replay()
+    torch.cuda.synchronize()
+    samples = []
+    for _ in range(5):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        graph.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        samples.append(e0.elapsed_time(e1) * 1e3)
+    return sorted(samples)[len(samples) // 2]
+
+
+_flush_graph_us = None
+
+
+def _device_time(fn, cold):
+    """Device time per call in us, free of the Python wrapper's host work: GRAPH_REPS calls captured in one CUDA
+    graph (each preceded by an L2-evicting fill when ``cold``), minus the same graph with the fills alone."""
+    global _flush_graph_us
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        fn()
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    with torch.cuda.graph(graph):
+        for _ in range(GRAPH_REPS):
+            if cold:
+                flush.zero_()
+            fn()
+    total = _replay_us(graph)
+    if cold:
+        if _flush_graph_us is None:
+            only = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(only):
+                for _ in range(GRAPH_REPS):
+                    flush.zero_()
+            _flush_graph_us = _replay_us(only)
+        total -= _flush_graph_us
+    return total / GRAPH_REPS
+
+
+def timed(name, fn, bytes_moved=None, flops=None, cold=True, capturable=True):
+    """``us``: device time per call (CUDA-graph replay, no host work inside the measurement); ``us_eager``: the call
+    as the framework's eager paths see it, Python wrapper included (events around one call after a synchronize)."""
     for _ in range(3):
         fn()
     times = []
@@ -43,8 +93,15 @@ def timed(name, fn, bytes_moved=None, flops=None, cold=True):
         torch.cuda.synchronize()
         times.append(e0.elapsed_time(e1) * 1e3)
     times.sort()
-    us = times[len(times) // 2]
-    entry = {"us": round(us, 2)}
+    eager = times[len(times) // 2]
+    try:
+        if not capturable:
+            raise NotImplementedError("host work inside the call")
+        us, how = _device_time(fn, cold), "graph"
+    except Exception as e:  # noqa: BLE001 -- an op that cannot be captured keeps its eager number
+        torch.cuda.synchronize()
+        us, how = eager, f"eager ({type(e).__name__})"
+    entry = {"us": round(us, 2), "us_eager": round(eager, 2), "timing": how}
     if bytes_moved:
         entry["GB/s"] = round(bytes_moved / us / 1e3, 1)
     if flops:
@@ -98,7 +155,8 @@ packed = [M.sign_pack(r) for r in rows]
 timed("sign_majority K=8", lambda: M.sign_majority(packed, P), bytes_moved=P * (8 * 0.125 + 4))
 timed("dropout_mask P=11.2M", lambda: M.dropout_mask(flat, 0.7, seed=1), bytes_moved=P * 8)
 block_of = torch.arange(len(layout.names), dtype=torch.int32, device=dev) // 3
-timed("block_sqdiff P=11.2M", lambda: M.block_sqdiff(flat, old, offsets, block_of, int(block_of.max()) + 1),
+n_blocks = int(block_of.max()) + 1
+timed("block_sqdiff P=11.2M", lambda: M.block_sqdiff(flat, old, offsets, block_of, n_blocks),
       bytes_moved=P * 8)
 
 for shape in [(64, 64, 32, 32), (64, 256, 8, 8), (64, 132, 32, 32)]:
@@ -111,7 +169,7 @@ for shape in [(64, 64, 32, 32), (64, 256, 8, 8), (64, 132, 32, 32)]:
         timed(f"bn_fwd+relu {shape}", lambda: B.bn_act(bn, x, relu=True), bytes_moved=elems * 2 * 2, cold=False)
     y = B.bn_act(bn, x, relu=True)
     timed(f"bn_bwd+relu {shape}", lambda: torch.autograd.grad(y, x, dy, retain_graph=True), bytes_moved=elems * 2 * 4,
-          cold=False)
+          cold=False, capturable=False)
 
 for (bsz, m, n, k) in [(1, 5000, 120, 400), (32, 5000, 120, 400), (32, 5000, 84, 120), (1, 8192, 4096, 4096)]:
     a = torch.randn(bsz, m, k, device=dev).bfloat16()
@@ -137,7 +195,7 @@ for (name, m, n, k, off) in [("fc1", 5000, 120, 400, 2572), ("conv2", 5000 * 100
         timed(f"subset_gemm {name} S={S_} NW={NW} {m}x{n}x{k} cluster={cl}",
               lambda: G.subset_linear(xa, arenas, ptable, coefs, off, off + n * k, n, k, relu=True,
                                       out_dtype=torch.bfloat16),
-              flops=2.0 * S_ * m * n * k, cold=False)
+              flops=2.0 * S_ * m * n * k, cold=False, capturable=False)
     os.environ.pop("DLS_SUBSET_CLUSTER")
     stride = (Pl + 63) // 64 * 64
     models = torch.empty(S_, stride, device=dev)[:, :Pl]
@@ -153,7 +211,7 @@ for (name, m, n, k, off) in [("fc1", 5000, 120, 400, 2572), ("conv2", 5000 * 100
         return G.linear_bf16(xa, w_b.contiguous(), models[:, off + n * k: off + n * k + n].contiguous(), relu=True,
                              out_dtype=torch.bfloat16)
 
-    timed(f"materialise + gemm {name} S={S_} NW={NW} {m}x{n}x{k}", two_step, flops=2.0 * S_ * m * n * k, cold=False)
+    timed(f"materialise + gemm {name} S={S_} NW={NW} {m}x{n}x{k}", two_step, flops=2.0 * S_ * m * n * k, cold=False, capturable=False)
 
 results["clocks"] = _clock_sampler.stop()  # SM clock / throttle record of this run
 print("clocks", results["clocks"], flush=True)
