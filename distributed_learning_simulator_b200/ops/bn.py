@@ -94,6 +94,7 @@ class _FusedBNAct(torch.autograd.Function):
                          dgamma.data_ptr(), dbeta.data_ptr(), ctx.bwd_partials.data_ptr(),
                          runtime.stream_ptr(x.device))
             STATS["bwd_acc"] += 1
+            ctx.bwd_partials = None  # the slice is dirty now: a second backward over this node takes the scratch path
             return dx, dgamma, dbeta, dres, None, None, None, None
         scratch = _scratch(rows, c, dtype, x.device)
         runtime.call("dls_bn_bwd", dy.data_ptr(), y.data_ptr(), x.data_ptr(), dtype, rows, c, weight.data_ptr(),
